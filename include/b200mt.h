@@ -1,0 +1,159 @@
+/*
+ * b200mt.h -- C ABI of libb200mt.so: the multi-tensor fused-optimizer hot path for B200 (sm_100a).
+ *
+ * This is the drop-in boundary.  Every entry point replaces one function of the reference's
+ * `amp_C` / `distributed_adam_cuda` / `fused_adam_cuda` pybind modules (cited per function as
+ * path:line under the reference tree).  Plain pointers and sizes only -- no torch / ATen types.
+ *
+ * Conventions
+ *  - A "tensor list set" is `depth` lists of `ntensors` device pointers each, passed list-major:
+ *    ptrs[d*ntensors + t] is tensor t of list d.  All lists share numel[t] (elements, int64).
+ *    The element type of list d is dtype[d] (B200MT_F32 ...).  Tensors must be dense; element 0
+ *    of tensor t is at ptrs[..]; there is no alignment requirement (misaligned views take a
+ *    peeled/scalar path).
+ *  - Every call is asynchronous on `stream` (a cudaStream_t passed as void*; NULL = legacy
+ *    default stream) of device `device`.  No call synchronises the host with the GPU.
+ *  - `noop` is a device pointer to one int32 (the reference's `noop_flag` / `_overflow_buf`).
+ *  - `chunk_size` keeps the reference's meaning where it is observable: the L2-norm kernels raise
+ *    `noop` when the sum of squares over one chunk of `chunk_size` elements is non-finite
+ *    (csrc/multi_tensor_l2norm_kernel.cu:99-108).  Work is scheduled in tiles that subdivide
+ *    chunks; element-wise ops ignore chunk_size apart from validating it (> 0).
+ *  - Return value: 0 on success, non-zero on error; b200mt_last_error() returns the message of
+ *    the last failing call on the calling thread.
+ *  - The library owns two kinds of internal device memory per device: the cache of tensor-list
+ *    descriptor tables (uploaded once per distinct list set, reused while pointers are
+ *    unchanged) and a per-stream scratch buffer for per-tile partial sums.  Both are created
+ *    lazily with cudaMalloc and released by b200mt_shutdown().
+ */
+#ifndef B200MT_H_
+#define B200MT_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { B200MT_F32 = 0, B200MT_F16 = 1, B200MT_BF16 = 2, B200MT_F64 = 3, B200MT_U8 = 4 };
+
+enum { B200MT_MAX_DEPTH = 5 };
+
+typedef struct b200mt_lists {
+  const void* const* ptrs;   /* depth*ntensors device pointers, list-major            */
+  const int64_t*     numel;  /* ntensors element counts                               */
+  int32_t            ntensors;
+  int32_t            depth;
+  int32_t            dtype[B200MT_MAX_DEPTH];
+  int32_t            device; /* CUDA device ordinal the tensors live on               */
+} b200mt_lists;
+
+/* ---- library ---------------------------------------------------------------------------- */
+const char* b200mt_last_error(void);
+int  b200mt_version(void);
+/* Number of kernels this library has launched since load (process-wide, all devices). */
+int64_t b200mt_launch_count(void);
+/* Descriptor-table cache statistics: uploads performed / cache hits. */
+int64_t b200mt_table_uploads(void);
+int64_t b200mt_table_hits(void);
+/* Tuning knobs (0 = keep default): elements per scheduling tile, CTAs per SM cap. */
+int  b200mt_set_tuning(int tile_elems, int grid_cap);
+/* Frees cached descriptor tables and scratch on every device.  Caller must have synchronised. */
+int  b200mt_shutdown(void);
+
+/* ---- amp_C.multi_tensor_scale  (csrc/multi_tensor_scale_kernel.cu:113-136, amp_C_frontend.cpp:3-7)
+ * lists = [in, out]; out = (out_t)((float)in * scale); *noop = 1 iff any input is inf/NaN.
+ * Never reads noop.  in may alias out. */
+int b200mt_scale(const b200mt_lists* lists, int chunk_size, int32_t* noop, float scale, void* stream);
+
+/* ---- amp_C.multi_tensor_axpby  (csrc/multi_tensor_axpby_kernel.cu:128-157)
+ * lists = [x, y, out]; out = a*x + b*y; arg_to_check: -1 both, 0 x, 1 y, anything else none. */
+int b200mt_axpby(const b200mt_lists* lists, int chunk_size, int32_t* noop, float a, float b,
+                 int arg_to_check, void* stream);
+
+/* ---- amp_C.multi_tensor_l2norm / _l2norm_mp / _l2norm_scale
+ *      (csrc/multi_tensor_l2norm_kernel.cu:301-364, multi_tensor_l2norm_kernel_mp.cu:153-216,
+ *       multi_tensor_l2norm_scale_kernel.cu:258-324)
+ * lists = [x]  (l2norm_scale: [in, out], out = in*scale written in the same pass).
+ * ret: device float[1] = sqrt(sum x^2);  ret_per_tensor: device float[ntensors] or NULL.
+ * Deterministic: per-tile partials are reduced in a fixed order by a second pass; no float atomics.
+ * flags: B200MT_NORM_NOOP_GATED makes every kernel return immediately when *noop != 0 and leaves
+ * ret / ret_per_tensor untouched (the _mp variant). */
+enum { B200MT_NORM_NOOP_GATED = 1 };
+int b200mt_l2norm(const b200mt_lists* lists, int chunk_size, int32_t* noop, float* ret,
+                  float* ret_per_tensor, int flags, void* stream);
+int b200mt_l2norm_scale(const b200mt_lists* lists, int chunk_size, int32_t* noop, float scale,
+                        float* ret, float* ret_per_tensor, void* stream);
+
+/* ---- amp_C.multi_tensor_adam  (csrc/multi_tensor_adam.cu:129-171)
+ * lists = [g, p, m, v] (one dtype for all four, as in the reference) or, as an extension,
+ * [g, p, m, v, p_copy] / mixed dtypes (g 16-bit, p/m/v fp32, p_copy 16-bit): a single fused
+ * read-modify-write pass.  mode 0 = L2 (decay added to g), 1 = AdamW.  Bias corrections are
+ * computed here on the host exactly as the reference does (1 - pow((double)beta, step) -> float).
+ * grad_scale multiplies g on load (1.0f = reference behaviour).  No noop interaction. */
+int b200mt_adam(const b200mt_lists* lists, int chunk_size, int32_t* noop, float lr, float beta1,
+                float beta2, float eps, int step, int mode, int bias_correction,
+                float weight_decay, float grad_scale, void* stream);
+
+/* ---- amp_C.multi_tensor_sgd  (csrc/multi_tensor_sgd_kernel.cu:141-322)
+ * lists = [g, p, mom] or [g, p, mom, p_model_fp16].  Returns immediately on the device when *noop. */
+int b200mt_sgd(const b200mt_lists* lists, int chunk_size, int32_t* noop, float wd, float momentum,
+               float dampening, float lr, int nesterov, int first_run, int wd_after_momentum,
+               float scale, void* stream);
+
+/* ---- amp_C.multi_tensor_lamb  (csrc/multi_tensor_lamb.cu:332-413)
+ * lists = [g, p, m, v], one dtype.  global_grad_norm: device float[1].  The per-tensor ||p|| and
+ * ||update|| partial sums are produced inside the stage-1 pass (two full reads fewer than the
+ * reference's four launches); g is overwritten with the update, as in the reference. */
+int b200mt_lamb(const b200mt_lists* lists, int chunk_size, int32_t* noop, float lr, float beta1,
+                float beta2, float eps, int step, int bias_correction, float weight_decay,
+                int grad_averaging, int mode, const float* global_grad_norm, float max_grad_norm,
+                int use_nvlamb, void* stream);
+
+/* ---- amp_C.multi_tensor_lamb_mp  (csrc/multi_tensor_lamb_mp.cu:367-496)
+ * lists = [g, p32, m32, v32] or [g, p32, m32, v32, p_model(g's dtype)].  lr, step, global_grad_norm,
+ * max_grad_norm, found_inf, inv_scale are device scalars (float / int32).  All kernels return
+ * immediately when *noop != 0. */
+int b200mt_lamb_mp(const b200mt_lists* lists, int chunk_size, int32_t* noop, const float* lr,
+                   float beta1, float beta2, float eps, const int32_t* step, int bias_correction,
+                   float weight_decay, int grad_averaging, int mode, const float* global_grad_norm,
+                   const float* max_grad_norm, int use_nvlamb, const float* found_inf,
+                   const float* inv_scale, void* stream);
+
+/* ---- amp_C.multi_tensor_lamb_stage1_cuda / stage2_cuda
+ *      (csrc/multi_tensor_lamb_stage_1.cu:112-151, csrc/multi_tensor_lamb_stage_2.cu:94-125)
+ * stage1 lists = [g, p, m, v, update]; per_tensor_decay: device float[ntensors];
+ * clipped_global_grad_norm is the host-side clip factor (reference dereferences a CPU tensor).
+ * stage2 lists = [p, update]; norms: device float[ntensors]. */
+int b200mt_lamb_stage1(const b200mt_lists* lists, int chunk_size, int32_t* noop,
+                       const float* per_tensor_decay, int step, float beta1, float beta2,
+                       float eps, float clipped_global_grad_norm, void* stream);
+int b200mt_lamb_stage2(const b200mt_lists* lists, int chunk_size, int32_t* noop,
+                       const float* per_tensor_param_norm, const float* per_tensor_update_norm,
+                       float lr, float weight_decay, int use_nvlamb, void* stream);
+
+/* ---- distributed_adam_cuda.multi_tensor_fused_adam
+ *      (apex/contrib/csrc/optimizers/multi_tensor_distopt_adam_kernel.cu:169-228)
+ * lists = [p32, m32, v32, g] or [p32, m32, v32, g, p_copy(g's dtype)].  Per-tensor device arrays
+ * beta1/beta2/eps/weight_decay (float[ntensors]) and bias_correction (int32[ntensors]).
+ * mode 0: eps inside sqrt, 1: outside. */
+int b200mt_dist_adam(const b200mt_lists* lists, int chunk_size, int32_t* noop,
+                     const float* per_tensor_beta1, const float* per_tensor_beta2,
+                     const int32_t* per_tensor_bias_correction, const float* per_tensor_eps,
+                     const float* per_tensor_weight_decay, float lr, float grad_scale, int step,
+                     int mode, void* stream);
+
+/* ---- fused_adam_cuda.adam_mt / maybe_cast_mt / strided_check_finite
+ *      (apex/contrib/csrc/optimizers/fused_adam_cuda_kernel.cu:283-387, :939-960, :785-812)
+ * adam_mt lists = [p, m, v, g] or [p, m, v, g, p_copy]; step_size form (eps not rescaled). */
+int b200mt_contrib_adam(const b200mt_lists* lists, int chunk_size, int32_t* noop, float lr,
+                        float beta1, float beta2, float eps, float grad_scale, int step, int mode,
+                        int bias_correction, float decay, void* stream);
+int b200mt_maybe_cast(const b200mt_lists* lists, int chunk_size, const int32_t* overflow_flag,
+                      void* stream);
+int b200mt_strided_check_finite(int32_t* noop, const void* p, int dtype, int64_t numel,
+                                int stride, int clear_overflow_first, int device, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200MT_H_ */

@@ -1,0 +1,69 @@
+#!/usr/bin/env bash
+# TEST INFRASTRUCTURE ONLY -- builds the *unmodified* reference kernels as a checker.
+#
+# Compiles the reference's own CUDA sources for the multi-tensor optimizer path, from where
+# they lie under /root/reference (nothing is copied into this repo), for sm_100a, into
+# oracle/_ref/ (git-ignored, but it travels to the GPU box with gpurun):
+#   amp_C_ref.so               <- csrc/multi_tensor_*.cu + csrc/amp_C_frontend.cpp
+#   distributed_adam_cuda_ref.so <- apex/contrib/csrc/optimizers/multi_tensor_distopt_adam*.{cpp,cu}
+#   fused_adam_cuda_ref.so     <- apex/contrib/csrc/optimizers/fused_adam_cuda*.{cpp,cu}
+# The reference's setup.py cannot be used (it shells out to /opt/rocm/bin/rocminfo at import,
+# setup.py:15-17), so this is a direct nvcc/g++ recipe with the flags setup.py:210 uses
+# (-O3 --use_fast_math -lineinfo + the VERSION_GE_* macros, setup.py:145-154).
+# Only tests/, __graft_entry__.smoke() and bench.py's comparison legs may load these.
+set -euo pipefail
+REF=${REF:-/root/reference}
+HERE="$(cd "$(dirname "$0")" && pwd)"
+OUT="$HERE/_ref"
+OBJ="$OUT/obj"
+if [ ! -d "$REF/csrc" ]; then
+  echo "[oracle/build_ref] $REF absent: keeping prebuilt oracle/_ref as is"; exit 0
+fi
+mkdir -p "$OBJ"
+PY=${PYTHON:-python}
+TORCH=$($PY -c 'import torch,os;print(os.path.dirname(torch.__file__))')
+PYINC=$($PY -c 'import sysconfig;print(sysconfig.get_paths()["include"])')
+INC="-I$REF/csrc -I$TORCH/include -I$TORCH/include/torch/csrc/api/include -I$PYINC -I/usr/local/cuda/include"
+DEFS="-DVERSION_GE_1_1 -DVERSION_GE_1_3 -DVERSION_GE_1_5 -DTORCH_API_INCLUDE_EXTENSION_H"
+NVFLAGS="-O3 -std=c++17 --use_fast_math -lineinfo --expt-relaxed-constexpr -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC -w"
+LIBS="-L$TORCH/lib -ltorch -ltorch_cpu -ltorch_cuda -lc10 -lc10_cuda -ltorch_python -L/usr/local/cuda/lib64 -lcudart -Wl,-rpath,$TORCH/lib"
+JOBS=${JOBS:-8}
+
+build_module () {   # name, then source files
+  local name=$1; shift
+  local objs=() pids=()
+  if [ -f "$OUT/$name.so" ] && [ -z "${FORCE:-}" ]; then echo "[oracle/build_ref] $name.so up to date"; return; fi
+  local running=0
+  for src in "$@"; do
+    local o="$OBJ/${name}_$(basename "${src%.*}").o"
+    objs+=("$o")
+    if [[ "$src" == *.cu ]]; then
+      nvcc -c "$src" -o "$o" $INC $DEFS -DTORCH_EXTENSION_NAME=$name $NVFLAGS &
+    else
+      g++ -c "$src" -o "$o" $INC $DEFS -DTORCH_EXTENSION_NAME=$name -O2 -std=c++17 -fPIC -w &
+    fi
+    pids+=($!)
+    running=$((running+1))
+    if [ $running -ge $JOBS ]; then wait -n; running=$((running-1)); fi
+  done
+  for p in "${pids[@]}"; do wait $p; done
+  g++ -shared "${objs[@]}" -o "$OUT/$name.so" $LIBS
+  echo "[oracle/build_ref] built $OUT/$name.so"
+}
+
+build_module amp_C_ref \
+  $REF/csrc/amp_C_frontend.cpp \
+  $REF/csrc/multi_tensor_scale_kernel.cu $REF/csrc/multi_tensor_axpby_kernel.cu \
+  $REF/csrc/multi_tensor_l2norm_kernel.cu $REF/csrc/multi_tensor_l2norm_kernel_mp.cu \
+  $REF/csrc/multi_tensor_l2norm_scale_kernel.cu $REF/csrc/multi_tensor_adam.cu \
+  $REF/csrc/multi_tensor_sgd_kernel.cu $REF/csrc/multi_tensor_lamb.cu \
+  $REF/csrc/multi_tensor_lamb_mp.cu $REF/csrc/multi_tensor_lamb_stage_1.cu \
+  $REF/csrc/multi_tensor_lamb_stage_2.cu $REF/csrc/multi_tensor_novograd.cu \
+  $REF/csrc/multi_tensor_adagrad.cu
+build_module distributed_adam_cuda_ref \
+  $REF/apex/contrib/csrc/optimizers/multi_tensor_distopt_adam.cpp \
+  $REF/apex/contrib/csrc/optimizers/multi_tensor_distopt_adam_kernel.cu
+build_module fused_adam_cuda_ref \
+  $REF/apex/contrib/csrc/optimizers/fused_adam_cuda.cpp \
+  $REF/apex/contrib/csrc/optimizers/fused_adam_cuda_kernel.cu
+rm -rf "$OBJ"

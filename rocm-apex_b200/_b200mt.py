@@ -1,0 +1,188 @@
+"""ctypes binding of libb200mt.so (declared in include/b200mt.h) plus the tensor-list packer.
+
+This is the only place where torch tensors are turned into the raw (pointer, numel, dtype) arrays
+the C ABI takes.  The checks performed while packing, and their messages, are the ones the
+reference's launch harness performs (csrc/multi_tensor_apply.cuh:53-70) so that callers and tests
+written against the reference see the same errors.
+
+There is no CPU path: importing this module without the built library raises immediately.
+"""
+import ctypes
+import os
+
+import numpy as np
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libb200mt.so")
+
+F32, F16, BF16, F64, U8 = 0, 1, 2, 3, 4
+MAX_DEPTH = 5
+NORM_NOOP_GATED = 1
+
+_DTYPE_CODE = {
+    torch.float32: F32,
+    torch.float16: F16,
+    torch.bfloat16: BF16,
+    torch.float64: F64,
+    torch.uint8: U8,
+}
+
+
+class Lists(ctypes.Structure):
+    _fields_ = [
+        ("ptrs", ctypes.c_void_p),
+        ("numel", ctypes.c_void_p),
+        ("ntensors", ctypes.c_int32),
+        ("depth", ctypes.c_int32),
+        ("dtype", ctypes.c_int32 * MAX_DEPTH),
+        ("device", ctypes.c_int32),
+    ]
+
+
+def _load():
+    if not os.path.exists(_LIB_PATH):
+        raise RuntimeError(
+            "libb200mt.so is not built (%s). Run `python -c 'import __graft_entry__ as g; g.build()'` "
+            "or `make -C rocm-apex_b200`. There is no CPU or PyTorch fallback for this path." % _LIB_PATH)
+    lib = ctypes.CDLL(_LIB_PATH)
+    c_int, c_float, vp = ctypes.c_int, ctypes.c_float, ctypes.c_void_p
+    LP = ctypes.POINTER(Lists)
+    sigs = {
+        "b200mt_last_error": (ctypes.c_char_p, []),
+        "b200mt_version": (c_int, []),
+        "b200mt_launch_count": (ctypes.c_int64, []),
+        "b200mt_table_uploads": (ctypes.c_int64, []),
+        "b200mt_table_hits": (ctypes.c_int64, []),
+        "b200mt_set_tuning": (c_int, [c_int, c_int]),
+        "b200mt_shutdown": (c_int, []),
+        "b200mt_scale": (c_int, [LP, c_int, vp, c_float, vp]),
+        "b200mt_axpby": (c_int, [LP, c_int, vp, c_float, c_float, c_int, vp]),
+        "b200mt_l2norm": (c_int, [LP, c_int, vp, vp, vp, c_int, vp]),
+        "b200mt_l2norm_scale": (c_int, [LP, c_int, vp, c_float, vp, vp, vp]),
+        "b200mt_adam": (c_int, [LP, c_int, vp, c_float, c_float, c_float, c_float, c_int, c_int, c_int,
+                                c_float, c_float, vp]),
+        "b200mt_sgd": (c_int, [LP, c_int, vp, c_float, c_float, c_float, c_float, c_int, c_int, c_int,
+                               c_float, vp]),
+        "b200mt_lamb": (c_int, [LP, c_int, vp, c_float, c_float, c_float, c_float, c_int, c_int, c_float,
+                                c_int, c_int, vp, c_float, c_int, vp]),
+        "b200mt_lamb_mp": (c_int, [LP, c_int, vp, vp, c_float, c_float, c_float, vp, c_int, c_float, c_int,
+                                   c_int, vp, vp, c_int, vp, vp, vp]),
+        "b200mt_lamb_stage1": (c_int, [LP, c_int, vp, vp, c_int, c_float, c_float, c_float, c_float, vp]),
+        "b200mt_lamb_stage2": (c_int, [LP, c_int, vp, vp, vp, c_float, c_float, c_int, vp]),
+        "b200mt_dist_adam": (c_int, [LP, c_int, vp, vp, vp, vp, vp, vp, c_float, c_float, c_int, c_int, vp]),
+        "b200mt_contrib_adam": (c_int, [LP, c_int, vp, c_float, c_float, c_float, c_float, c_float, c_int,
+                                        c_int, c_int, c_float, vp]),
+        "b200mt_maybe_cast": (c_int, [LP, c_int, vp, vp]),
+        "b200mt_strided_check_finite": (c_int, [vp, vp, c_int, ctypes.c_int64, c_int, c_int, c_int, vp]),
+    }
+    for name, (res, args) in sigs.items():
+        fn = getattr(lib, name)  # AttributeError here = header and library out of sync: fail loudly
+        fn.restype = res
+        fn.argtypes = args
+    return lib, tuple(sigs)
+
+
+lib, EXPORTS = _load()
+
+
+def check(rc):
+    """Turn a non-zero C return code into the RuntimeError the reference's TORCH_CHECK would raise."""
+    if rc != 0:
+        raise RuntimeError(lib.b200mt_last_error().decode("utf-8", "replace"))
+
+
+def dtype_code(t):
+    try:
+        return _DTYPE_CODE[t.dtype]
+    except KeyError:
+        raise RuntimeError("multi_tensor_apply not implemented for '%s'" % str(t.dtype).replace("torch.", ""))
+
+
+class Packed(object):
+    """A tensor-list set in C-ABI form.  Keeps the numpy arrays alive for the duration of the call."""
+    __slots__ = ("struct", "ptrs", "numel", "device", "ntensors", "depth")
+
+    def ref(self):
+        return ctypes.byref(self.struct)
+
+
+def pack(tensor_lists, depth=None):
+    """Validate `tensor_lists` like csrc/multi_tensor_apply.cuh:53-70 and build the C descriptor."""
+    nlists = len(tensor_lists)
+    if depth is not None:
+        ok = (nlists in depth) if isinstance(depth, (tuple, list)) else (nlists == depth)
+        if not ok:
+            raise RuntimeError("tensor_lists.size() != depth")
+    if nlists < 1 or nlists > MAX_DEPTH:
+        raise RuntimeError("tensor_lists.size() != depth")
+    first = tensor_lists[0]
+    ntensors = len(first)
+    if ntensors <= 0:
+        raise RuntimeError("tensor_lists[0].size() is not > 0")
+    ref_device = first[0].device
+    if ref_device.type != "cuda":
+        raise RuntimeError("expected input to be on cuda")
+    ptrs = np.empty(nlists * ntensors, dtype=np.uint64)
+    numel = np.empty(ntensors, dtype=np.int64)
+    for t in range(ntensors):
+        numel[t] = first[t].numel()
+    k = 0
+    for lst in tensor_lists:
+        if len(lst) != ntensors:
+            raise RuntimeError("Size mismatch among tensor lists")
+        dt = lst[0].dtype
+        for t, x in enumerate(lst):
+            if x.is_sparse:
+                raise RuntimeError("sparse tensors are not supported on this path")
+            if not (x.is_contiguous() or (x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last))
+                    or (x.dim() == 5 and x.is_contiguous(memory_format=torch.channels_last_3d))):
+                raise RuntimeError("A tensor was not contiguous.")
+            if x.device != ref_device:
+                raise RuntimeError("A tensor was not on the same device as the first tensor")
+            if x.numel() != numel[t]:
+                raise RuntimeError("Size mismatch")
+            if x.dtype != dt:
+                raise RuntimeError("tensors of one list must share a dtype (tensor %d)" % t)
+            ptrs[k] = x.data_ptr()
+            k += 1
+    p = Packed()
+    p.ptrs, p.numel = ptrs, numel
+    p.ntensors, p.depth = ntensors, nlists
+    p.device = ref_device.index if ref_device.index is not None else torch.cuda.current_device()
+    s = Lists()
+    s.ptrs = ptrs.ctypes.data
+    s.numel = numel.ctypes.data
+    s.ntensors = ntensors
+    s.depth = nlists
+    for d, lst in enumerate(tensor_lists):
+        s.dtype[d] = dtype_code(lst[0])
+    s.device = p.device
+    p.struct = s
+    return p
+
+
+def stream_ptr(device_index):
+    """cudaStream_t of torch's current stream on the tensors' device (the reference launches on
+    at::cuda::getCurrentCUDAStream() under a device guard, csrc/multi_tensor_apply.cuh:78-79)."""
+    return torch.cuda.current_stream(device_index).cuda_stream
+
+
+def dev_ptr(t, dtype=None, what="tensor"):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("expected %s to be on cuda" % what)
+    if dtype is not None and t.dtype != dtype:
+        raise RuntimeError("expected %s to have dtype %s, got %s" % (what, dtype, t.dtype))
+    return t.data_ptr()
+
+
+def noop_ptr(noop_flag, device_index=None):
+    if not noop_flag.is_cuda:
+        raise RuntimeError("expected noop flag to be on cuda")
+    if noop_flag.dtype != torch.int32:
+        raise RuntimeError("expected noop flag to be an int32 tensor")
+    if device_index is not None and noop_flag.device.index != device_index:
+        raise RuntimeError("expected noop flag to be on the same device as tensors")
+    return noop_flag.data_ptr()

@@ -1,0 +1,376 @@
+// mt_device.cuh -- device side of the multi-tensor launch: descriptor-table view, tile walk,
+// vectorised streaming loop and deterministic CTA reductions.  sm_100a only.
+//
+// Replaces (and is deliberately not shaped like) the reference harness
+// csrc/multi_tensor_apply.cuh:19-42: there, <=110 tensor addresses and <=320 (tensor, chunk)
+// records ride in a ~3 KB by-value kernel argument and a list needs many launches.  Here the
+// tensor list lives in a device-resident table (uploaded once, reused while pointers are
+// unchanged), ONE launch covers any number of tensors, and every CTA finds its tile with a
+// binary search over a per-tensor tile prefix.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <type_traits>
+#include <tuple>
+
+namespace b200mt {
+
+// ------------------------------------------------------------------------------------------
+// Descriptor table as the kernels see it (all pointers are device pointers into one blob).
+// ------------------------------------------------------------------------------------------
+struct TableView {
+  const unsigned long long* ptrs;   // [depth][ntensors] base addresses, list-major
+  const long long*          numel;  // [ntensors]
+  const int*                tile_prefix;  // [ntensors+1] exclusive prefix of tiles per tensor
+  int       ntensors;
+  int       ntiles;
+  int       tile_elems;   // elements per scheduling tile
+  int       ppc;          // tiles per full chunk (1 for element-wise ops)
+  long long chunk_elems;  // chunk length in elements (== tile_elems when ppc == 1)
+};
+
+struct TileLoc {
+  int       tensor;
+  int       chunk;   // chunk index inside the tensor (== tile index inside tensor when ppc==1)
+  long long off;     // element offset of the tile inside the tensor
+  int       len;     // elements in the tile
+};
+
+__device__ __forceinline__ TileLoc locate_tile(const TableView& tv, int tile) {
+  // upper_bound(tile_prefix, tile) - 1 : last tensor whose first tile is <= tile.  Empty tensors
+  // have zero tiles and can never be selected.
+  int lo = 0, hi = tv.ntensors;  // invariant: prefix[lo] <= tile < prefix[hi]
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (__ldg(tv.tile_prefix + mid) <= tile) lo = mid; else hi = mid;
+  }
+  TileLoc L;
+  L.tensor = lo;
+  const int local = tile - __ldg(tv.tile_prefix + lo);
+  const long long n = __ldg(tv.numel + lo);
+  const int chunk = local / tv.ppc;
+  const int piece = local - chunk * tv.ppc;
+  L.chunk = chunk;
+  L.off = (long long)chunk * tv.chunk_elems + (long long)piece * tv.tile_elems;
+  long long chunk_end = (long long)(chunk + 1) * tv.chunk_elems;
+  if (chunk_end > n) chunk_end = n;
+  long long len = chunk_end - L.off;
+  if (len > tv.tile_elems) len = tv.tile_elems;
+  L.len = (int)len;
+  return L;
+}
+
+// ------------------------------------------------------------------------------------------
+// Element types: 4-element ("quad") vector access + scalar access, everything widened to fp32.
+// Streaming cache policy: loads and stores do not allocate in L1 (no reuse on this path).
+// ------------------------------------------------------------------------------------------
+#ifndef B200MT_CACHE_POLICY
+#define B200MT_CACHE_POLICY 1   // 0: default caching, 1: L1::no_allocate, 2: .cs (evict-first)
+#endif
+
+__device__ __forceinline__ float4 ld_f4(const float4* p) {
+  float4 r;
+#if B200MT_CACHE_POLICY == 1
+  asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+#elif B200MT_CACHE_POLICY == 2
+  r = __ldcs(p);
+#else
+  r = *p;
+#endif
+  return r;
+}
+__device__ __forceinline__ void st_f4(float4* p, float4 v) {
+#if B200MT_CACHE_POLICY == 1
+  asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+#elif B200MT_CACHE_POLICY == 2
+  __stcs(p, v);
+#else
+  *p = v;
+#endif
+}
+__device__ __forceinline__ uint2 ld_u2(const uint2* p) {
+  uint2 r;
+#if B200MT_CACHE_POLICY == 1
+  asm volatile("ld.global.L1::no_allocate.v2.u32 {%0,%1}, [%2];"
+               : "=r"(r.x), "=r"(r.y) : "l"(p) : "memory");
+#elif B200MT_CACHE_POLICY == 2
+  r = __ldcs(p);
+#else
+  r = *p;
+#endif
+  return r;
+}
+__device__ __forceinline__ void st_u2(uint2* p, uint2 v) {
+#if B200MT_CACHE_POLICY == 1
+  asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};"
+               :: "l"(p), "r"(v.x), "r"(v.y) : "memory");
+#elif B200MT_CACHE_POLICY == 2
+  __stcs(p, v);
+#else
+  *p = v;
+#endif
+}
+
+template <typename T> struct Elem;
+
+template <> struct Elem<float> {
+  static constexpr int SIZE = 4, QUAD_ALIGN = 16;
+  static __device__ __forceinline__ void ld4(const void* p, float (&r)[4]) {
+    float4 v = ld_f4(reinterpret_cast<const float4*>(p));
+    r[0] = v.x; r[1] = v.y; r[2] = v.z; r[3] = v.w;
+  }
+  static __device__ __forceinline__ void st4(void* p, const float (&r)[4]) {
+    st_f4(reinterpret_cast<float4*>(p), make_float4(r[0], r[1], r[2], r[3]));
+  }
+  static __device__ __forceinline__ float ld1(const void* p) { return *reinterpret_cast<const float*>(p); }
+  static __device__ __forceinline__ void st1(void* p, float v) { *reinterpret_cast<float*>(p) = v; }
+  static __device__ __forceinline__ float round_trip(float v) { return v; }
+};
+
+template <> struct Elem<__half> {
+  static constexpr int SIZE = 2, QUAD_ALIGN = 8;
+  static __device__ __forceinline__ void ld4(const void* p, float (&r)[4]) {
+    uint2 v = ld_u2(reinterpret_cast<const uint2*>(p));
+    float2 a = __half22float2(*reinterpret_cast<__half2*>(&v.x));
+    float2 b = __half22float2(*reinterpret_cast<__half2*>(&v.y));
+    r[0] = a.x; r[1] = a.y; r[2] = b.x; r[3] = b.y;
+  }
+  static __device__ __forceinline__ void st4(void* p, const float (&r)[4]) {
+    __half2 a = __floats2half2_rn(r[0], r[1]);
+    __half2 b = __floats2half2_rn(r[2], r[3]);
+    uint2 v;
+    v.x = *reinterpret_cast<unsigned*>(&a);
+    v.y = *reinterpret_cast<unsigned*>(&b);
+    st_u2(reinterpret_cast<uint2*>(p), v);
+  }
+  static __device__ __forceinline__ float ld1(const void* p) { return __half2float(*reinterpret_cast<const __half*>(p)); }
+  static __device__ __forceinline__ void st1(void* p, float v) { *reinterpret_cast<__half*>(p) = __float2half_rn(v); }
+  static __device__ __forceinline__ float round_trip(float v) { return __half2float(__float2half_rn(v)); }
+};
+
+template <> struct Elem<__nv_bfloat16> {
+  static constexpr int SIZE = 2, QUAD_ALIGN = 8;
+  static __device__ __forceinline__ void ld4(const void* p, float (&r)[4]) {
+    uint2 v = ld_u2(reinterpret_cast<const uint2*>(p));
+    // bf16 -> fp32 is a 16-bit left shift
+    r[0] = __uint_as_float(v.x << 16); r[1] = __uint_as_float(v.x & 0xffff0000u);
+    r[2] = __uint_as_float(v.y << 16); r[3] = __uint_as_float(v.y & 0xffff0000u);
+  }
+  static __device__ __forceinline__ void st4(void* p, const float (&r)[4]) {
+    __nv_bfloat162 a = __floats2bfloat162_rn(r[0], r[1]);
+    __nv_bfloat162 b = __floats2bfloat162_rn(r[2], r[3]);
+    uint2 v;
+    v.x = *reinterpret_cast<unsigned*>(&a);
+    v.y = *reinterpret_cast<unsigned*>(&b);
+    st_u2(reinterpret_cast<uint2*>(p), v);
+  }
+  static __device__ __forceinline__ float ld1(const void* p) { return __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(p)); }
+  static __device__ __forceinline__ void st1(void* p, float v) { *reinterpret_cast<__nv_bfloat16*>(p) = __float2bfloat16_rn(v); }
+  static __device__ __forceinline__ float round_trip(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+};
+
+// fp64 lists (multi_tensor_adam accepts them): arithmetic stays fp32 as in the reference
+// (MATH_T = float, csrc/multi_tensor_adam.cu:19), so a quad is four 8-byte accesses.
+template <> struct Elem<double> {
+  static constexpr int SIZE = 8, QUAD_ALIGN = 8;
+  static __device__ __forceinline__ void ld4(const void* p, float (&r)[4]) {
+    const double* d = reinterpret_cast<const double*>(p);
+#pragma unroll
+    for (int i = 0; i < 4; i++) r[i] = (float)d[i];
+  }
+  static __device__ __forceinline__ void st4(void* p, const float (&r)[4]) {
+    double* d = reinterpret_cast<double*>(p);
+#pragma unroll
+    for (int i = 0; i < 4; i++) d[i] = (double)r[i];
+  }
+  static __device__ __forceinline__ float ld1(const void* p) { return (float)*reinterpret_cast<const double*>(p); }
+  static __device__ __forceinline__ void st1(void* p, float v) { *reinterpret_cast<double*>(p) = (double)v; }
+  static __device__ __forceinline__ float round_trip(float v) { return v; }
+};
+
+// compile-time loop
+template <int N, int I = 0, class F>
+__device__ __forceinline__ void static_for(F&& f) {
+  if constexpr (I < N) {
+    f(std::integral_constant<int, I>{});
+    static_for<N, I + 1>(f);
+  }
+}
+
+template <typename... Ts> struct TypeList {
+  static constexpr int size = sizeof...(Ts);
+  template <int K> using at = typename std::tuple_element<K, std::tuple<Ts...>>::type;
+};
+
+// ------------------------------------------------------------------------------------------
+// Deterministic CTA-wide sum: xor-shuffle inside each warp, one shared-memory hop, then the
+// first warp reduces the per-warp values in a fixed order.  Result valid in thread 0.
+// All threads of the CTA must call it.
+// ------------------------------------------------------------------------------------------
+template <int THREADS>
+__device__ __forceinline__ float cta_sum(float v, float* smem /* >= THREADS/32 floats */) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int NW = THREADS / 32;
+  __syncthreads();  // protect smem reuse across consecutive calls
+  if (lane == 0) smem[warp] = v;
+  __syncthreads();
+  float r = 0.f;
+  if (warp == 0) {
+    r = (lane < NW) ? smem[lane] : 0.f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+  }
+  return r;
+}
+
+// ------------------------------------------------------------------------------------------
+// The streaming kernel.  Op supplies:
+//   using Types = TypeList<...>;            element type of every list
+//   static constexpr int THREADS, UNROLL, MIN_CTAS;
+//   static constexpr unsigned STORES;       bit k set: list k is written back
+//   struct State;                           per-thread registers
+//   bool  begin(State&) const;              false: whole kernel is a no-op (noop gating)
+//   unsigned load_mask() const;             bit k set: list k is read (others arrive as 0.f)
+//   unsigned store_mask() const;            run-time subset of STORES (default: all of STORES)
+//   void  tile_begin(State&, const TileLoc&) const;
+//   void  elem(State&, float (&x)[NL]) const;      the per-element math, fp32 registers
+//   void  tile_end(State&, int tile, const TileLoc&, float* smem) const;   (CTA-uniform)
+//   void  end(State&) const;
+// ------------------------------------------------------------------------------------------
+template <class Op>
+__global__ void __launch_bounds__(Op::THREADS, Op::MIN_CTAS)
+mt_stream_kernel(const TableView tv, const Op op) {
+  using Types = typename Op::Types;
+  constexpr int NL = Types::size;
+  constexpr int THREADS = Op::THREADS;
+  constexpr int U = Op::UNROLL;
+  __shared__ float red_smem[THREADS / 32];
+
+  typename Op::State st;
+  if (!op.begin(st)) return;
+  const unsigned lmask = op.load_mask();
+  const unsigned smask = op.store_mask();
+  const int tid = threadIdx.x;
+
+  for (int tile = blockIdx.x; tile < tv.ntiles; tile += gridDim.x) {
+    const TileLoc L = locate_tile(tv, tile);
+    op.tile_begin(st, L);
+
+    // base address of this tile in every list + common head peel to reach quad alignment
+    char* base[NL];
+    int head = -1;
+    bool vec_ok = true;
+    static_for<NL>([&](auto k) {
+      using T = typename Types::template at<k.value>;
+      unsigned long long a = __ldg(tv.ptrs + (size_t)k.value * tv.ntensors + L.tensor);
+      a += (unsigned long long)L.off * Elem<T>::SIZE;
+      base[k.value] = reinterpret_cast<char*>(a);
+      constexpr int P = Elem<T>::QUAD_ALIGN / Elem<T>::SIZE;  // alignment period in elements
+      if constexpr (P > 1) {
+        const int mis = (int)(a % Elem<T>::QUAD_ALIGN) / Elem<T>::SIZE;  // elements past a boundary
+        const int hk = (P - mis) % P;
+        static_assert(P == 4, "all vectorised element types have a 4-element period");
+        if (head < 0) head = hk; else vec_ok = vec_ok && (head == hk);
+      }
+    });
+    if (head < 0) head = 0;
+    if (!vec_ok || head > L.len) head = L.len;  // phases disagree: whole tile on the scalar path
+    const int nq = (L.len - head) >> 2;
+    const int tail0 = head + (nq << 2);
+
+    // ---- vector body: UNROLL quads per thread in flight, all loads issued before any math
+    for (int q0 = 0; q0 < nq; q0 += THREADS * U) {
+      float x[U][NL][4];
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const int q = q0 + tid + u * THREADS;
+        if (q < nq) {
+          static_for<NL>([&](auto k) {
+            using T = typename Types::template at<k.value>;
+            if (lmask & (1u << k.value)) {
+              Elem<T>::ld4(base[k.value] + ((size_t)head + ((size_t)q << 2)) * Elem<T>::SIZE, x[u][k.value]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 4; i++) x[u][k.value][i] = 0.f;
+            }
+          });
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const int q = q0 + tid + u * THREADS;
+        if (q < nq) {
+#pragma unroll
+          for (int i = 0; i < 4; i++) {
+            float e[NL];
+#pragma unroll
+            for (int k = 0; k < NL; k++) e[k] = x[u][k][i];
+            op.elem(st, e);
+#pragma unroll
+            for (int k = 0; k < NL; k++) x[u][k][i] = e[k];
+          }
+          static_for<NL>([&](auto k) {
+            using T = typename Types::template at<k.value>;
+            if constexpr ((Op::STORES >> k.value) & 1u) {
+              if (smask & (1u << k.value))
+                Elem<T>::st4(base[k.value] + ((size_t)head + ((size_t)q << 2)) * Elem<T>::SIZE, x[u][k.value]);
+            }
+          });
+        }
+      }
+    }
+
+    // ---- scalar head/tail (<= 6 elements when vectorised, the whole tile otherwise)
+    const int nscalar = head + (L.len - tail0);
+    for (int s = tid; s < nscalar; s += THREADS) {
+      const int i = (s < head) ? s : (tail0 + (s - head));
+      float e[NL];
+      static_for<NL>([&](auto k) {
+        using T = typename Types::template at<k.value>;
+        e[k.value] = (lmask & (1u << k.value)) ? Elem<T>::ld1(base[k.value] + (size_t)i * Elem<T>::SIZE) : 0.f;
+      });
+      op.elem(st, e);
+      static_for<NL>([&](auto k) {
+        using T = typename Types::template at<k.value>;
+        if constexpr ((Op::STORES >> k.value) & 1u) {
+          if (smask & (1u << k.value))
+            Elem<T>::st1(base[k.value] + (size_t)i * Elem<T>::SIZE, e[k.value]);
+        }
+      });
+    }
+
+    op.tile_end(st, tile, L, red_smem);
+  }
+  op.end(st);
+}
+
+// 1 - beta^step evaluated in double and narrowed, as the reference's device-side
+// `1 - std::pow(beta, step)` does (std::pow(float, int) promotes to double;
+// csrc/multi_tensor_lamb_mp.cu:66-70, multi_tensor_distopt_adam_kernel.cu:59-63).  The value is tiny
+// for beta2 at small steps, so fp32 powf would lose ~1e-4 relative.  Lane 0 computes, warp broadcasts.
+__device__ __forceinline__ float bias_correction_dev(float beta, int step) {
+  float r = 0.f;
+  if ((threadIdx.x & 31) == 0) r = (float)(1.0 - pow((double)beta, (double)step));
+  return __shfl_sync(0xffffffffu, r, 0);
+}
+
+// Default no-op hooks an Op can inherit.
+struct OpBase {
+  struct State {};
+  static constexpr int THREADS = 256;
+  static constexpr int UNROLL = 4;
+  static constexpr int MIN_CTAS = 4;
+  __device__ __forceinline__ unsigned store_mask() const { return 0xffffffffu; }
+  template <class S> __device__ __forceinline__ bool begin(S&) const { return true; }
+  template <class S> __device__ __forceinline__ void tile_begin(S&, const TileLoc&) const {}
+  template <class S> __device__ __forceinline__ void tile_end(S&, int, const TileLoc&, float*) const {}
+  template <class S> __device__ __forceinline__ void end(S&) const {}
+};
+
+}  // namespace b200mt

@@ -1,0 +1,322 @@
+// mt_host.cu -- library state of libb200mt.so: errors, descriptor-table cache, scratch.
+#include "mt_host.h"
+
+#include <atomic>
+#include <climits>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <vector>
+
+namespace b200mt {
+
+// ---------------------------------------------------------------------------------------------
+// errors, counters, tuning
+// ---------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+static std::atomic<int64_t> g_launches{0}, g_uploads{0}, g_hits{0};
+static std::recursive_mutex g_mu;
+static int g_tile_elems = 0;  // 0 = not yet initialised
+static int g_grid_cap = 0;    // 0 = one CTA per tile
+
+int set_error(const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return 1;
+}
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+const char* dtype_name(int d) {
+  switch (d) {
+    case B200MT_F32: return "Float";
+    case B200MT_F16: return "Half";
+    case B200MT_BF16: return "BFloat16";
+    case B200MT_F64: return "Double";
+    case B200MT_U8: return "Byte";
+    default: return "Unknown";
+  }
+}
+
+static void init_tuning() {
+  if (g_tile_elems) return;
+  g_tile_elems = 8192;
+  if (const char* e = getenv("B200MT_TILE_ELEMS")) { int v = atoi(e); if (v >= 64) g_tile_elems = v; }
+  if (const char* e = getenv("B200MT_GRID_CAP")) { int v = atoi(e); if (v > 0) g_grid_cap = v; }
+}
+
+Tiling elementwise_tiling() {
+  init_tuning();
+  Tiling t; t.tile_elems = g_tile_elems; t.ppc = 1; t.chunk_elems = g_tile_elems; return t;
+}
+
+Tiling chunked_tiling(int chunk_size) {
+  init_tuning();
+  Tiling t;
+  t.chunk_elems = chunk_size;
+  if (chunk_size <= g_tile_elems) { t.tile_elems = chunk_size; t.ppc = 1; return t; }
+  int ppc = (chunk_size + g_tile_elems - 1) / g_tile_elems;
+  int tile = (chunk_size + ppc - 1) / ppc;
+  tile = (tile + 15) & ~15;  // keep interior tile boundaries 16-element aligned
+  t.ppc = (chunk_size + tile - 1) / tile;
+  t.tile_elems = tile;
+  return t;
+}
+
+int grid_for(int ntiles) {
+  if (g_grid_cap > 0 && ntiles > g_grid_cap) return g_grid_cap;
+  return ntiles;
+}
+
+// ---------------------------------------------------------------------------------------------
+// per-device context
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int kSlots = 64;
+constexpr int kMaxDevices = 64;
+
+struct Slot {
+  bool valid = false;
+  uint64_t hash = 0;
+  size_t bytes = 0;   // image size
+  size_t cap = 0;     // capacity of host/dev buffers
+  char* host = nullptr;  // pinned shadow of the image
+  char* dev = nullptr;
+  cudaEvent_t uploaded = nullptr;
+  std::vector<cudaStream_t> users;  // streams that may still be reading `dev`
+  uint64_t tick = 0;
+};
+
+struct StreamScratch { void* ptr = nullptr; size_t cap = 0; };
+
+struct DevCtx {
+  Slot slots[kSlots];
+  std::map<cudaStream_t, StreamScratch> scratch;
+  std::vector<void*> retired;   // outgrown scratch buffers, possibly still in flight
+  cudaEvent_t tmp_ev = nullptr;
+  uint64_t tick = 0;
+};
+
+DevCtx* g_ctx[kMaxDevices] = {nullptr};
+
+struct ImageHeader {
+  uint32_t magic, depth, ntensors, tile_elems, ppc, ntiles;
+  int64_t chunk_elems;
+};
+
+thread_local std::vector<char> g_staging;
+
+inline uint64_t hash_words(const char* p, size_t bytes) {
+  // FNV-1a over 64-bit words (image size is always a multiple of 8)
+  uint64_t h = 1469598103934665603ull;
+  const uint64_t* w = reinterpret_cast<const uint64_t*>(p);
+  for (size_t i = 0, n = bytes / 8; i < n; i++) { h ^= w[i]; h *= 1099511628211ull; }
+  return h;
+}
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+CallGuard::CallGuard(int dev) : status(0), prev_device(-1), device(dev) {
+  g_mu.lock();
+  if (dev < 0 || dev >= kMaxDevices) { status = set_error("invalid device ordinal %d", dev); return; }
+  cudaError_t e = cudaGetDevice(&prev_device);
+  if (e != cudaSuccess) { status = set_error("CUDA error: %s (cudaGetDevice)", cudaGetErrorString(e)); return; }
+  if (prev_device != dev) {
+    e = cudaSetDevice(dev);
+    if (e != cudaSuccess) { status = set_error("CUDA error: %s (cudaSetDevice %d)", cudaGetErrorString(e), dev); return; }
+  }
+}
+CallGuard::~CallGuard() {
+  if (prev_device >= 0 && prev_device != device) cudaSetDevice(prev_device);
+  g_mu.unlock();
+}
+
+static DevCtx* ctx_for_current_device(int device) {
+  if (!g_ctx[device]) g_ctx[device] = new DevCtx();
+  return g_ctx[device];
+}
+
+int check_common(const b200mt_lists* L, int chunk_size) {
+  B200MT_CHECK(L != nullptr, "lists is NULL");
+  B200MT_CHECK(chunk_size > 0, "chunk_size must be > 0 (got %d)", chunk_size);
+  B200MT_CHECK(L->depth >= 1 && L->depth <= B200MT_MAX_DEPTH, "tensor_lists.size() != depth");
+  B200MT_CHECK(L->ntensors > 0, "tensor_lists[0].size() is not > 0");
+  B200MT_CHECK(L->ptrs != nullptr && L->numel != nullptr, "lists->ptrs / lists->numel is NULL");
+  return 0;
+}
+
+int acquire_table(const b200mt_lists* L, int dmin, int dmax, const Tiling& tiling,
+                  cudaStream_t stream, TableView* out) {
+  B200MT_CHECK(L->depth >= dmin && L->depth <= dmax, "tensor_lists.size() != depth");
+  const int T = L->ntensors, D = L->depth;
+  DevCtx* ctx = ctx_for_current_device(L->device);
+
+  // ---- build the image in host staging memory
+  const size_t off_ptrs = sizeof(ImageHeader);
+  const size_t off_numel = off_ptrs + (size_t)D * T * 8;
+  const size_t off_prefix = off_numel + (size_t)T * 8;
+  const size_t bytes = align_up(off_prefix + (size_t)(T + 1) * 4, 16);
+  if (g_staging.size() < bytes) g_staging.resize(bytes);
+  char* img = g_staging.data();
+  memset(img + off_prefix, 0, bytes - off_prefix);
+  memcpy(img + off_ptrs, L->ptrs, (size_t)D * T * 8);
+  memcpy(img + off_numel, L->numel, (size_t)T * 8);
+  int* prefix = reinterpret_cast<int*>(img + off_prefix);
+  long long acc = 0;
+  for (int t = 0; t < T; t++) {
+    const long long n = L->numel[t];
+    B200MT_CHECK(n >= 0, "negative numel for tensor %d", t);
+    if (n > 0)
+      for (int d = 0; d < D; d++)
+        B200MT_CHECK(L->ptrs[(size_t)d * T + t] != nullptr, "NULL data pointer (list %d, tensor %d)", d, t);
+    prefix[t] = (int)acc;
+    const long long full = n / tiling.chunk_elems, rem = n % tiling.chunk_elems;
+    acc += full * tiling.ppc + (rem + tiling.tile_elems - 1) / tiling.tile_elems;
+    B200MT_CHECK(acc < INT_MAX, "tensor list too large: more than 2^31 tiles");
+  }
+  prefix[T] = (int)acc;
+  ImageHeader* h = reinterpret_cast<ImageHeader*>(img);
+  h->magic = 0xb200;
+  h->depth = D; h->ntensors = T; h->tile_elems = tiling.tile_elems; h->ppc = tiling.ppc;
+  h->ntiles = (uint32_t)acc; h->chunk_elems = tiling.chunk_elems;
+  const uint64_t hash = hash_words(img, bytes);
+
+  // ---- look it up
+  Slot* slot = nullptr;
+  for (int i = 0; i < kSlots; i++) {
+    Slot& s = ctx->slots[i];
+    if (s.valid && s.hash == hash && s.bytes == bytes && memcmp(s.host, img, bytes) == 0) { slot = &s; break; }
+  }
+  if (slot) {
+    g_hits.fetch_add(1, std::memory_order_relaxed);
+    bool known = false;
+    for (cudaStream_t u : slot->users) known = known || (u == stream);
+    if (!known) {  // first use on this stream: order after the upload
+      B200MT_CUDA(cudaStreamWaitEvent(stream, slot->uploaded, 0));
+      slot->users.push_back(stream);
+    }
+  } else {
+    // evict the least recently used slot
+    slot = &ctx->slots[0];
+    for (int i = 0; i < kSlots; i++) {
+      Slot& s = ctx->slots[i];
+      if (!s.valid) { slot = &s; break; }
+      if (s.tick < slot->tick) slot = &s;
+    }
+    if (!ctx->tmp_ev) B200MT_CUDA(cudaEventCreateWithFlags(&ctx->tmp_ev, cudaEventDisableTiming));
+    if (!slot->uploaded) B200MT_CUDA(cudaEventCreateWithFlags(&slot->uploaded, cudaEventDisableTiming));
+    if (slot->valid) {
+      // (a) the pinned shadow may still be the source of an in-flight upload
+      B200MT_CUDA(cudaEventSynchronize(slot->uploaded));
+      // (b) kernels on other streams may still read the device copy: order this stream after them
+      for (cudaStream_t u : slot->users) {
+        if (u == stream) continue;
+        B200MT_CUDA(cudaEventRecord(ctx->tmp_ev, u));
+        B200MT_CUDA(cudaStreamWaitEvent(stream, ctx->tmp_ev, 0));
+      }
+    }
+    slot->valid = false;
+    slot->users.clear();
+    if (slot->cap < bytes) {
+      // Growing: the old device buffer may be read by kernels on this stream -> retire, don't free.
+      if (slot->dev) ctx->retired.push_back(slot->dev);
+      if (slot->host) cudaFreeHost(slot->host);
+      slot->host = slot->dev = nullptr; slot->cap = 0;
+      size_t cap = 16384;
+      while (cap < bytes) cap *= 2;
+      B200MT_CUDA(cudaHostAlloc((void**)&slot->host, cap, cudaHostAllocDefault));
+      B200MT_CUDA(cudaMalloc((void**)&slot->dev, cap));
+      slot->cap = cap;
+    }
+    memcpy(slot->host, img, bytes);
+    B200MT_CUDA(cudaMemcpyAsync(slot->dev, slot->host, bytes, cudaMemcpyHostToDevice, stream));
+    B200MT_CUDA(cudaEventRecord(slot->uploaded, stream));
+    slot->hash = hash; slot->bytes = bytes; slot->valid = true;
+    slot->users.push_back(stream);
+    g_uploads.fetch_add(1, std::memory_order_relaxed);
+  }
+  slot->tick = ++ctx->tick;
+
+  out->ptrs = reinterpret_cast<const unsigned long long*>(slot->dev + off_ptrs);
+  out->numel = reinterpret_cast<const long long*>(slot->dev + off_numel);
+  out->tile_prefix = reinterpret_cast<const int*>(slot->dev + off_prefix);
+  out->ntensors = T;
+  out->ntiles = (int)acc;
+  out->tile_elems = tiling.tile_elems;
+  out->ppc = tiling.ppc;
+  out->chunk_elems = tiling.chunk_elems;
+  return 0;
+}
+
+int acquire_scratch(cudaStream_t stream, size_t bytes, void** out) {
+  int device = 0;
+  B200MT_CUDA(cudaGetDevice(&device));
+  DevCtx* ctx = ctx_for_current_device(device);
+  StreamScratch& s = ctx->scratch[stream];
+  if (s.cap < bytes) {
+    if (s.ptr) ctx->retired.push_back(s.ptr);  // may still be in flight on this stream
+    size_t cap = 1 << 20;
+    while (cap < bytes) cap *= 2;
+    s.ptr = nullptr; s.cap = 0;
+    B200MT_CUDA(cudaMalloc(&s.ptr, cap));
+    s.cap = cap;
+    B200MT_CUDA(cudaMemsetAsync(s.ptr, 0, 256, stream));
+  }
+  *out = s.ptr;
+  return 0;
+}
+
+}  // namespace b200mt
+
+// ---------------------------------------------------------------------------------------------
+// C ABI: library-level entry points
+// ---------------------------------------------------------------------------------------------
+using namespace b200mt;
+
+extern "C" const char* b200mt_last_error(void) { return g_err.c_str(); }
+extern "C" int b200mt_version(void) { return 100; }
+extern "C" int64_t b200mt_launch_count(void) { return g_launches.load(); }
+extern "C" int64_t b200mt_table_uploads(void) { return g_uploads.load(); }
+extern "C" int64_t b200mt_table_hits(void) { return g_hits.load(); }
+
+extern "C" int b200mt_set_tuning(int tile_elems, int grid_cap) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  init_tuning();
+  if (tile_elems > 0) {
+    B200MT_CHECK(tile_elems >= 64 && tile_elems % 16 == 0, "tile_elems must be a multiple of 16, >= 64");
+    g_tile_elems = tile_elems;
+  }
+  if (grid_cap >= 0) g_grid_cap = grid_cap;
+  return 0;
+}
+
+extern "C" int b200mt_shutdown(void) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  int prev = -1;
+  cudaGetDevice(&prev);
+  for (int d = 0; d < kMaxDevices; d++) {
+    DevCtx* c = g_ctx[d];
+    if (!c) continue;
+    cudaSetDevice(d);
+    for (int i = 0; i < kSlots; i++) {
+      Slot& s = c->slots[i];
+      if (s.dev) cudaFree(s.dev);
+      if (s.host) cudaFreeHost(s.host);
+      if (s.uploaded) cudaEventDestroy(s.uploaded);
+    }
+    for (auto& kv : c->scratch) if (kv.second.ptr) cudaFree(kv.second.ptr);
+    for (void* p : c->retired) cudaFree(p);
+    if (c->tmp_ev) cudaEventDestroy(c->tmp_ev);
+    delete c;
+    g_ctx[d] = nullptr;
+  }
+  if (prev >= 0) cudaSetDevice(prev);
+  return 0;
+}

@@ -1,0 +1,79 @@
+// mt_host.h -- host side shared by every op of libb200mt.so: error reporting, the per-device
+// cache of descriptor tables, per-stream scratch, and the launch helper.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string>
+
+#include "../../include/b200mt.h"
+#include "mt_device.cuh"
+
+namespace b200mt {
+
+// ---- errors --------------------------------------------------------------------------------
+int  set_error(const char* fmt, ...);          // stores message (thread-local), returns 1
+void count_launch(int n = 1);
+
+#define B200MT_CUDA(expr)                                                                   \
+  do {                                                                                      \
+    cudaError_t e__ = (expr);                                                               \
+    if (e__ != cudaSuccess)                                                                 \
+      return ::b200mt::set_error("CUDA error: %s (%s) at %s:%d", cudaGetErrorString(e__),   \
+                                 #expr, __FILE__, __LINE__);                                \
+  } while (0)
+
+#define B200MT_CHECK(cond, ...)                                                             \
+  do {                                                                                      \
+    if (!(cond)) return ::b200mt::set_error(__VA_ARGS__);                                   \
+  } while (0)
+
+const char* dtype_name(int dtype);
+
+// ---- per-call guard: takes the library lock, switches to lists->device, restores on exit ----
+struct CallGuard {
+  explicit CallGuard(int device);
+  ~CallGuard();
+  int status;  // 0 ok
+  int prev_device;
+  int device;
+};
+
+// ---- tiling policy -------------------------------------------------------------------------
+struct Tiling {
+  int       tile_elems;
+  int       ppc;
+  long long chunk_elems;
+};
+// Element-wise ops: chunk_size has no observable effect, tiles subdivide the tensor directly.
+Tiling elementwise_tiling();
+// Norm ops: a chunk of `chunk_size` elements is split into ppc tiles so that the per-chunk
+// overflow check of the reference (csrc/multi_tensor_l2norm_kernel.cu:103) is preserved.
+Tiling chunked_tiling(int chunk_size);
+
+// Validates the list set (depth, counts, null pointers) and returns a device-resident table for
+// it on `stream`, uploading only when no cached copy matches.
+int acquire_table(const b200mt_lists* L, int expect_depth_min, int expect_depth_max,
+                  const Tiling& tiling, cudaStream_t stream, TableView* out);
+
+// Per-(device, stream) scratch of at least `bytes` bytes, 256-byte aligned, contents undefined
+// except for the first 256 bytes which are zero at creation and which every user must leave
+// zero (they hold self-resetting completion counters).
+int acquire_scratch(cudaStream_t stream, size_t bytes, void** out);
+
+int grid_for(int ntiles);
+
+template <class Op>
+int launch_stream(const TableView& tv, const Op& op, cudaStream_t stream) {
+  if (tv.ntiles <= 0) return 0;
+  mt_stream_kernel<Op><<<grid_for(tv.ntiles), Op::THREADS, 0, stream>>>(tv, op);
+  count_launch();
+  B200MT_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// common argument checks shared by all entry points
+int check_common(const b200mt_lists* L, int chunk_size);
+
+}  // namespace b200mt

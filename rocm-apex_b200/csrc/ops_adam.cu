@@ -1,0 +1,233 @@
+// ops_adam.cu -- Adam / AdamW updates.
+//   b200mt_adam         <- amp_C.multi_tensor_adam (csrc/multi_tensor_adam.cu:23-171)
+//   b200mt_dist_adam    <- distributed_adam_cuda.multi_tensor_fused_adam
+//                          (apex/contrib/csrc/optimizers/multi_tensor_distopt_adam_kernel.cu:32-228)
+//   b200mt_contrib_adam <- fused_adam_cuda.adam_mt
+//                          (apex/contrib/csrc/optimizers/fused_adam_cuda_kernel.cu:74-200,283-387)
+// All three are one fused read-modify-write pass: every list is read once and written once with
+// 128-bit accesses (the reference's multi_tensor_adam has no vector path at all, :66-125).
+#include <cmath>
+#include "mt_dispatch.h"
+
+namespace b200mt {
+
+// ---- amp_C.multi_tensor_adam ------------------------------------------------------------------
+// lists [g, p, m, v] (+ optional p_copy).  Per-element math follows
+// csrc/multi_tensor_adam.cu:94-112 in fp32 with IEEE division / sqrt.
+template <typename Tg, typename Tp, typename Tc, bool COPY>
+struct AdamOp : OpBase {
+  using Types = typename std::conditional<COPY, TypeList<Tg, Tp, Tp, Tp, Tc>, TypeList<Tg, Tp, Tp, Tp>>::type;
+  static constexpr int NL = COPY ? 5 : 4;
+  static constexpr unsigned STORES = COPY ? 0b11110 : 0b01110;
+  static constexpr int UNROLL = 2;
+  static constexpr int THREADS = 256;
+  static constexpr int MIN_CTAS = 4;
+  float beta1, beta2, bc1, bc2, eps, lr, decay, grad_scale;
+  int mode;
+  __device__ __forceinline__ unsigned load_mask() const { return 0b01111; }
+  __device__ __forceinline__ void elem(State&, float (&x)[NL]) const {
+    float g = x[0] * grad_scale, p = x[1], m = x[2], v = x[3];
+    if (mode == 0) {  // L2: decay folded into the gradient
+      g = g + decay * p;
+      m = beta1 * m + (1.f - beta1) * g;
+      v = beta2 * v + (1.f - beta2) * g * g;
+      const float mu = m / bc1, vu = v / bc2;
+      const float denom = sqrtf(vu) + eps;
+      p = p - lr * (mu / denom);
+    } else {          // AdamW: decoupled decay
+      m = beta1 * m + (1.f - beta1) * g;
+      v = beta2 * v + (1.f - beta2) * g * g;
+      const float mu = m / bc1, vu = v / bc2;
+      const float denom = sqrtf(vu) + eps;
+      p = p - lr * (mu / denom + decay * p);
+    }
+    x[1] = p; x[2] = m; x[3] = v;
+    if constexpr (COPY) x[4] = p;
+  }
+};
+
+// ---- distributed_adam_cuda.multi_tensor_fused_adam ---------------------------------------------
+// lists [p32, m32, v32, g] (+ p_copy in g's dtype); per-tensor hyper-parameters in device arrays;
+// bias correction evaluated on the device per tile from `step`
+// (multi_tensor_distopt_adam_kernel.cu:54-63,103-116).
+template <typename Tg, bool COPY>
+struct DistAdamOp : OpBase {
+  using Types = typename std::conditional<COPY, TypeList<float, float, float, Tg, Tg>, TypeList<float, float, float, Tg>>::type;
+  static constexpr int NL = COPY ? 5 : 4;
+  static constexpr unsigned STORES = COPY ? 0b10111 : 0b00111;
+  static constexpr int UNROLL = 2;
+  static constexpr int THREADS = 256;
+  static constexpr int MIN_CTAS = 4;
+  struct State { float b1, b2, eps, decay, bc1, bc2; };
+  const float *pt_beta1, *pt_beta2, *pt_eps, *pt_decay;
+  const int* pt_bias_correction;
+  float lr, grad_scale;
+  int step, mode;
+  __device__ __forceinline__ unsigned load_mask() const { return 0b01111; }
+  __device__ __forceinline__ void tile_begin(State& s, const TileLoc& L) const {
+    const int t = L.tensor;
+    s.b1 = __ldg(pt_beta1 + t); s.b2 = __ldg(pt_beta2 + t);
+    s.eps = __ldg(pt_eps + t); s.decay = __ldg(pt_decay + t);
+    if (__ldg(pt_bias_correction + t) == 1) {
+      s.bc1 = bias_correction_dev(s.b1, step);
+      s.bc2 = bias_correction_dev(s.b2, step);
+    } else {
+      s.bc1 = 1.f; s.bc2 = 1.f;
+    }
+  }
+  __device__ __forceinline__ void elem(State& s, float (&x)[NL]) const {
+    float p = x[0], m = x[1], v = x[2];
+    const float g = x[3] / grad_scale;
+    m = s.b1 * m + (1.f - s.b1) * g;
+    v = s.b2 * v + (1.f - s.b2) * g * g;
+    const float mu = m / s.bc1, vu = v / s.bc2;
+    const float denom = (mode == 0) ? sqrtf(vu + s.eps) : sqrtf(vu) + s.eps;
+    p = p - lr * (mu / denom + s.decay * p);
+    x[0] = p; x[1] = m; x[2] = v;
+    if constexpr (COPY) x[4] = p;
+  }
+};
+
+// ---- fused_adam_cuda.adam_mt --------------------------------------------------------------------
+// lists [p, m, v, g] (+ p_copy); step_size = lr*sqrt(bc2)/bc1 on the host, eps not rescaled
+// (fused_adam_cuda_kernel.cu:131-146,298-306).
+template <typename Tp, typename Tg, bool COPY>
+struct ContribAdamOp : OpBase {
+  using Types = typename std::conditional<COPY, TypeList<Tp, Tp, Tp, Tg, Tg>, TypeList<Tp, Tp, Tp, Tg>>::type;
+  static constexpr int NL = COPY ? 5 : 4;
+  static constexpr unsigned STORES = COPY ? 0b10111 : 0b00111;
+  static constexpr int UNROLL = 2;
+  static constexpr int THREADS = 256;
+  static constexpr int MIN_CTAS = 4;
+  float b1, b2, eps, grad_scale, step_size, decay;
+  int mode;
+  __device__ __forceinline__ unsigned load_mask() const { return 0b01111; }
+  __device__ __forceinline__ void elem(State&, float (&x)[NL]) const {
+    float p = x[0], m = x[1], v = x[2];
+    const float g = x[3] / grad_scale;
+    m = b1 * m + (1.f - b1) * g;
+    v = b2 * v + (1.f - b2) * g * g;
+    const float denom = (mode == 0) ? sqrtf(v + eps) : sqrtf(v) + eps;
+    const float update = (m / denom) + (decay * p);
+    p = p - (step_size * update);
+    x[0] = p; x[1] = m; x[2] = v;
+    if constexpr (COPY) x[4] = p;
+  }
+};
+
+}  // namespace b200mt
+
+using namespace b200mt;
+
+extern "C" int b200mt_adam(const b200mt_lists* L, int chunk_size, int32_t* noop, float lr, float beta1,
+                           float beta2, float eps, int step, int mode, int bias_correction,
+                           float weight_decay, float grad_scale, void* stream_) {
+  (void)noop;  // multi_tensor_adam never touches the flag
+  if (check_common(L, chunk_size)) return 1;
+  CallGuard guard(L->device);
+  if (guard.status) return 1;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  TableView tv;
+  if (acquire_table(L, 4, 5, elementwise_tiling(), stream, &tv)) return 1;
+
+  // host-side bias correction, evaluated in double and narrowed (csrc/multi_tensor_adam.cu:145-149)
+  float bc1 = 1.f, bc2 = 1.f;
+  if (bias_correction == 1) {
+    bc1 = (float)(1.0 - std::pow((double)beta1, (double)step));
+    bc2 = (float)(1.0 - std::pow((double)beta2, (double)step));
+  }
+  auto fill = [&](auto& op) {
+    op.beta1 = beta1; op.beta2 = beta2; op.bc1 = bc1; op.bc2 = bc2; op.eps = eps; op.lr = lr;
+    op.decay = weight_decay; op.grad_scale = grad_scale; op.mode = mode;
+  };
+  const int dg = L->dtype[0], dp = L->dtype[1];
+  B200MT_CHECK(L->dtype[2] == dp && L->dtype[3] == dp, "adam: p, m and v must share one dtype");
+  if (L->depth == 4) {
+    if (dg == dp) {  // the reference's case: one dtype for all four lists
+      return dispatch_f64_f32_f16_bf16(dg, "adam", [&](auto t) {
+        using T = typename decltype(t)::type;
+        AdamOp<T, T, T, false> op; fill(op);
+        return launch_stream(tv, op, stream);
+      });
+    }
+    B200MT_CHECK(dp == B200MT_F32, "adam: mixed-precision lists need fp32 p/m/v");
+    return dispatch_f32_f16_bf16(dg, "adam", [&](auto t) {
+      using T = typename decltype(t)::type;
+      AdamOp<T, float, T, false> op; fill(op);
+      return launch_stream(tv, op, stream);
+    });
+  }
+  // depth 5: [g, p32, m32, v32, p_copy] single-pass mixed precision
+  B200MT_CHECK(dp == B200MT_F32, "adam: the 5-list form needs fp32 p/m/v");
+  const int dc = L->dtype[4];
+  B200MT_CHECK(dc == B200MT_F16 || dc == B200MT_BF16, "adam: p_copy must be Half or BFloat16");
+  return dispatch_f32_f16_bf16(dg, "adam", [&](auto tg) {
+    using Tg = typename decltype(tg)::type;
+    if (dc == B200MT_F16) { AdamOp<Tg, float, __half, true> op; fill(op); return launch_stream(tv, op, stream); }
+    AdamOp<Tg, float, __nv_bfloat16, true> op; fill(op);
+    return launch_stream(tv, op, stream);
+  });
+}
+
+extern "C" int b200mt_dist_adam(const b200mt_lists* L, int chunk_size, int32_t* noop,
+                                const float* pt_beta1, const float* pt_beta2,
+                                const int32_t* pt_bias_correction, const float* pt_eps,
+                                const float* pt_weight_decay, float lr, float grad_scale, int step,
+                                int mode, void* stream_) {
+  (void)noop;
+  if (check_common(L, chunk_size)) return 1;
+  B200MT_CHECK(pt_beta1 && pt_beta2 && pt_bias_correction && pt_eps && pt_weight_decay,
+               "per-tensor hyper-parameter array is NULL");
+  CallGuard guard(L->device);
+  if (guard.status) return 1;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  TableView tv;
+  if (acquire_table(L, 4, 5, elementwise_tiling(), stream, &tv)) return 1;
+  B200MT_CHECK(L->dtype[0] == B200MT_F32 && L->dtype[1] == B200MT_F32 && L->dtype[2] == B200MT_F32,
+               "dist_adam: p, m, v must be fp32");
+  B200MT_CHECK(L->depth == 4 || L->dtype[4] == L->dtype[3], "dist_adam: p_copy must have the gradient dtype");
+  auto fill = [&](auto& op) {
+    op.pt_beta1 = pt_beta1; op.pt_beta2 = pt_beta2; op.pt_eps = pt_eps; op.pt_decay = pt_weight_decay;
+    op.pt_bias_correction = pt_bias_correction; op.lr = lr; op.grad_scale = grad_scale;
+    op.step = step; op.mode = mode;
+  };
+  return dispatch_f32_f16_bf16(L->dtype[3], "dist_adam_cuda_kernel", [&](auto tg) {
+    using Tg = typename decltype(tg)::type;
+    if (L->depth == 5) { DistAdamOp<Tg, true> op; fill(op); return launch_stream(tv, op, stream); }
+    DistAdamOp<Tg, false> op; fill(op);
+    return launch_stream(tv, op, stream);
+  });
+}
+
+extern "C" int b200mt_contrib_adam(const b200mt_lists* L, int chunk_size, int32_t* noop, float lr,
+                                   float beta1, float beta2, float eps, float grad_scale, int step,
+                                   int mode, int bias_correction, float decay, void* stream_) {
+  (void)noop;
+  if (check_common(L, chunk_size)) return 1;
+  CallGuard guard(L->device);
+  if (guard.status) return 1;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  TableView tv;
+  if (acquire_table(L, 4, 5, elementwise_tiling(), stream, &tv)) return 1;
+  // fused_adam_cuda_kernel.cu:298-306
+  float step_size = lr;
+  if (bias_correction == 1) {
+    const float bc1 = 1.f - std::pow(beta1, step);
+    const float bc2 = 1.f - std::pow(beta2, step);
+    step_size = lr * std::sqrt(bc2) / bc1;
+  }
+  const int dp = L->dtype[0], dg = L->dtype[3];
+  B200MT_CHECK(L->dtype[1] == dp && L->dtype[2] == dp, "adam_mt: p, m, v must share one dtype");
+  B200MT_CHECK(L->depth == 4 || L->dtype[4] == dg, "adam_mt: p_copy must have the gradient dtype");
+  auto fill = [&](auto& op) {
+    op.b1 = beta1; op.b2 = beta2; op.eps = eps; op.grad_scale = grad_scale; op.step_size = step_size;
+    op.decay = decay; op.mode = mode;
+  };
+  B200MT_CHECK(dp == B200MT_F32, "adam_mt: p, m, v must be fp32");
+  return dispatch_f32_f16_bf16(dg, "adam_cuda_mt_kernel", [&](auto tg) {
+    using Tg = typename decltype(tg)::type;
+    if (L->depth == 5) { ContribAdamOp<float, Tg, true> op; fill(op); return launch_stream(tv, op, stream); }
+    ContribAdamOp<float, Tg, false> op; fill(op);
+    return launch_stream(tv, op, stream);
+  });
+}

@@ -1,0 +1,25 @@
+"""Drop-in `distributed_adam_cuda` (apex/contrib/csrc/optimizers/multi_tensor_distopt_adam.cpp:3-20):
+the shard-local fused AdamW step of the ZeRO-style DistributedFusedAdam."""
+import torch
+
+import _b200mt as _mt
+
+_lib = _mt.lib
+
+
+def multi_tensor_fused_adam(chunk_size, noop_flag, tensor_lists, per_tensor_beta1, per_tensor_beta2,
+                            per_tensor_bias_correction, per_tensor_eps, per_tensor_weight_decay, lr, grad_scale,
+                            step, mode):
+    """tensor_lists = [p32, m32, v32, g(, p_copy)]; per-tensor hyper-parameters are device arrays
+    (multi_tensor_distopt_adam_kernel.cu:169-228).  mode 0: eps inside sqrt, 1: outside."""
+    if len(tensor_lists) not in (4, 5):
+        raise RuntimeError("expected tensor lists of size 4 or 5")
+    L = _mt.pack(tensor_lists, (4, 5))
+    _mt.check(_lib.b200mt_dist_adam(
+        L.ref(), int(chunk_size), _mt.noop_ptr(noop_flag),
+        _mt.dev_ptr(per_tensor_beta1, torch.float32, "per_tensor_beta1"),
+        _mt.dev_ptr(per_tensor_beta2, torch.float32, "per_tensor_beta2"),
+        _mt.dev_ptr(per_tensor_bias_correction, torch.int32, "per_tensor_bias_correction"),
+        _mt.dev_ptr(per_tensor_eps, torch.float32, "per_tensor_eps"),
+        _mt.dev_ptr(per_tensor_weight_decay, torch.float32, "per_tensor_weight_decay"),
+        float(lr), float(grad_scale), int(step), int(mode), _mt.stream_ptr(L.device)))

@@ -1,0 +1,50 @@
+"""Drop-in `fused_adam_cuda` (apex/contrib/csrc/optimizers/fused_adam_cuda.cpp:78-86), restricted to
+the entry points the sharded hot path uses: adam_mt, maybe_cast_mt, strided_check_finite."""
+import torch
+
+import _b200mt as _mt
+
+_lib = _mt.lib
+
+
+def adam_mt(chunk_size, overflow_flag, tensor_lists, lr, beta1, beta2, eps, grad_scale, step, mode,
+            bias_correction, decay):
+    """tensor_lists = [p, m, v, g(, p_copy)], step_size = lr*sqrt(bc2)/bc1 form
+    (fused_adam_cuda_kernel.cu:283-387)."""
+    if len(tensor_lists) not in (4, 5):
+        raise RuntimeError("expected tensor lists of size 4 or 5")
+    L = _mt.pack(tensor_lists, (4, 5))
+    _mt.check(_lib.b200mt_contrib_adam(L.ref(), int(chunk_size), _mt.noop_ptr(overflow_flag), float(lr),
+                                       float(beta1), float(beta2), float(eps), float(grad_scale), int(step),
+                                       int(mode), int(bias_correction), float(decay), _mt.stream_ptr(L.device)))
+
+
+def maybe_cast_mt(chunk_size, overflow_flag, tensor_lists):
+    """tensor_lists = [p_in, p_out]; out = (out dtype)in unless the flag is set (:939-960)."""
+    if len(tensor_lists) != 2:
+        raise RuntimeError("expected tensor lists of size 2")
+    L = _mt.pack(tensor_lists, 2)
+    _mt.check(_lib.b200mt_maybe_cast(L.ref(), int(chunk_size), _mt.noop_ptr(overflow_flag),
+                                     _mt.stream_ptr(L.device)))
+
+
+def strided_check_finite(overflow_flag, p_copy, stride, clear_overflow_first):
+    """Tests every stride-th element of p_copy; optionally clears the flag first (:785-812)."""
+    if not p_copy.is_cuda or not p_copy.is_contiguous():
+        raise RuntimeError("p_copy must be a contiguous CUDA tensor")
+    dev = p_copy.device.index
+    _mt.check(_lib.b200mt_strided_check_finite(_mt.noop_ptr(overflow_flag), p_copy.data_ptr(),
+                                               _mt.dtype_code(p_copy), p_copy.numel(), int(stride),
+                                               int(clear_overflow_first), dev, _mt.stream_ptr(dev)))
+
+
+def _unsupported(name):
+    def f(*a, **k):
+        raise NotImplementedError("fused_adam_cuda.%s is outside the hot path (SURVEY.md 8f-4)" % name)
+    return f
+
+
+adam = _unsupported("adam")
+reversible_adam = _unsupported("reversible_adam")
+maybe_adam_undo = _unsupported("maybe_adam_undo")
+maybe_cast = _unsupported("maybe_cast")

@@ -1,0 +1,57 @@
+"""Shared helpers for the parity tests."""
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_DIR = os.path.join(ROOT, "oracle", "_ref")
+
+
+def load_ref(name):
+    """Import one of the reference's own kernels compiled unmodified into oracle/_ref
+    (oracle/build_ref.sh).  Returns None when it was not built."""
+    path = os.path.join(REF_DIR, name + ".so")
+    if not os.path.exists(path):
+        return None
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def rel_err(a, b, floor=1e-30):
+    """max |a-b| / max(|b|, floor) over elements, both widened to fp64; nan/inf must coincide."""
+    a = a.detach().double().cpu().reshape(-1)
+    b = b.detach().double().cpu().reshape(-1)
+    fa, fb = torch.isfinite(a), torch.isfinite(b)
+    if not torch.equal(fa, fb):
+        return float("inf")
+    if not torch.equal(a[~fa].isnan(), b[~fb].isnan()):
+        return float("inf")
+    a, b = a[fa], b[fb]
+    if a.numel() == 0:
+        return 0.0
+    return float(((a - b).abs() / b.abs().clamp_min(floor)).max())
+
+
+def assert_close_rel(a, b, rtol, atol=0.0, what=""):
+    """|a-b| <= atol + rtol*|b| element-wise (fp64 compare)."""
+    a64 = a.detach().double().cpu().reshape(-1)
+    b64 = b.detach().double().cpu().reshape(-1)
+    assert a64.shape == b64.shape, what
+    fin = torch.isfinite(b64)
+    assert torch.equal(torch.isfinite(a64), fin), "%s: finiteness differs" % what
+    err = (a64[fin] - b64[fin]).abs()
+    bound = atol + rtol * b64[fin].abs()
+    bad = err > bound
+    if bad.any():
+        i = int(torch.nonzero(bad)[0])
+        raise AssertionError("%s: %d/%d elements outside rtol=%g atol=%g; first: got %r want %r" % (
+            what, int(bad.sum()), err.numel(), rtol, atol, float(a64[fin][i]), float(b64[fin][i])))
+
+
+def resnet50_shapes():
+    import param_shapes
+    return param_shapes.resnet50()
