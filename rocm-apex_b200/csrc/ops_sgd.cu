@@ -36,8 +36,10 @@ struct SgdOp : OpBase {
       else g = mo;
     }
     if (wd != 0.f && wd_after) g += wd * w;
-    // `weight += -lr*g` evaluated in fp32 and rounded once to the weight's storage type
-    const float wn = Elem<Tw>::round_trip(w + (-lr * g));
+    // `weight_in[i] += (-lr * g)` on a Half/BFloat16 weight first converts the increment to the
+    // weight's type (c10's operator+= takes a Half), then adds in fp32 and rounds again; for fp32
+    // weights both conversions are the identity (csrc/multi_tensor_sgd_kernel.cu:124).
+    const float wn = Elem<Tw>::round_trip(w + Elem<Tw>::round_trip(-lr * g));
     x[1] = wn;
     x[2] = mo;
     if constexpr (COPY) x[3] = wn;  // the reference re-reads the stored weight for the fp16 copy
