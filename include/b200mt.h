@@ -153,6 +153,29 @@ int b200mt_maybe_cast(const b200mt_lists* lists, int chunk_size, const int32_t* 
 int b200mt_strided_check_finite(int32_t* noop, const void* p, int dtype, int64_t numel,
                                 int stride, int clear_overflow_first, int device, void* stream);
 
+/* ---- b200mt_l2norm_flat_noalloc -- no counterpart in the reference.
+ * L2 norm of ONE flat device buffer (x, dtype, numel) with the same two-pass arithmetic and the same
+ * per-chunk overflow flag as b200mt_l2norm, for hosts that cannot let this library allocate: a
+ * process whose GPU memory has already been handed in full to another runtime's pool (a cudaMalloc
+ * from here would fail), or a step loop that must never run into cudaMalloc's device-wide
+ * synchronisation.  It calls no cudaMalloc / cudaHostAlloc / cudaFree and creates no events; its
+ * working memory is a fixed array inside the library image:
+ *   - B200MT_NOALLOC_SCRATCH_BYTES of device memory are held on every GPU that loads the library,
+ *     until the process exits;
+ *   - inputs that need more than B200MT_NOALLOC_MAX_TILES scheduling tiles are refused with an error
+ *     (536,870,912 elements at the default 8192-element tile with chunk_size >= 8192; fewer for
+ *     smaller chunk sizes);
+ *   - all calls on a device share the array: calls whose GPU work may overlap (unordered streams)
+ *     race and must be ordered by the caller; back-to-back calls on one stream are safe, the
+ *     function re-zeroes what has to start at zero;
+ *   - the first call on each device queries the array's device address (host-side, nothing is
+ *     allocated): make that call before starting any stream capture on that device.
+ * ret: device float[1].  *noop is set when a chunk's sum of squares is inf/NaN. */
+#define B200MT_NOALLOC_MAX_TILES 65536
+#define B200MT_NOALLOC_SCRATCH_BYTES (512 + 4 * (B200MT_NOALLOC_MAX_TILES + 2) + 248)
+int b200mt_l2norm_flat_noalloc(const void* x, int dtype, int64_t numel, int chunk_size,
+                               int32_t* noop, float* ret, int device, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -75,6 +75,7 @@ def _load():
                                         c_int, c_int, c_float, vp]),
         "b200mt_maybe_cast": (c_int, [LP, c_int, vp, vp]),
         "b200mt_strided_check_finite": (c_int, [vp, vp, c_int, ctypes.c_int64, c_int, c_int, c_int, vp]),
+        "b200mt_l2norm_flat_noalloc": (c_int, [vp, c_int, ctypes.c_int64, c_int, vp, vp, c_int, vp]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)  # AttributeError here = header and library out of sync: fail loudly
