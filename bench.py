@@ -268,7 +268,10 @@ def run_single(args):
             traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
         except Exception:
             traffic = None
-    cpu = cpu_reference_run(steps=40, warmup=2, max_seconds=20.0)
+    if os.environ.get("B200MT_BENCH_SKIP_CPU"):   # profiling runs only: keep the command short under ncu
+        cpu = {"value": None, "cores": 0, "steps": 0, "host_cpus": os.cpu_count(), "ms_per_step": None}
+    else:
+        cpu = cpu_reference_run(steps=40, warmup=2, max_seconds=20.0)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -163,8 +163,8 @@ int b200mt_strided_check_finite(int32_t* noop, const void* p, int dtype, int64_t
  *   - B200MT_NOALLOC_SCRATCH_BYTES of device memory are held on every GPU that loads the library,
  *     until the process exits;
  *   - inputs that need more than B200MT_NOALLOC_MAX_TILES scheduling tiles are refused with an error
- *     (536,870,912 elements at the default 8192-element tile with chunk_size >= 8192; fewer for
- *     smaller chunk sizes);
+ *     (268,435,456 elements at the default 4096-element tile with chunk_size >= 4096; fewer for
+ *     smaller chunk sizes, more with a larger B200MT_TILE_ELEMS);
  *   - all calls on a device share the array: calls whose GPU work may overlap (unordered streams)
  *     race and must be ordered by the caller; back-to-back calls on one stream are safe, the
  *     function re-zeroes what has to start at zero;

@@ -1,0 +1,324 @@
+"""DistributedFusedAdam: ZeRO-style sharded AdamW for one NVSwitch domain.
+
+Same public surface as the reference (apex/contrib/optimizers/distributed_fused_adam.py:8-636):
+constructor keywords, set_global_scale / global_scale, complete_reductions(), step(), L2_grad_norm,
+has_overflow / peek_overflow, strided_check_finite(), state_dict() = {step, fp32_p, fp32_m, fp32_v}
+(this rank's shards).  The pipeline is the reference's --
+
+    gradients --(predivide 1/W, flatten)--> flat grads --reduce-scatter--> grad shard
+        --> shard-local fused Adam (distributed_adam_cuda.multi_tensor_fused_adam, writes fp32 p/m/v and the
+            low-precision p_copy in one pass) --> all-gather of p_copy --> model parameters
+
+-- but laid out for 8 B200 behind one NVSwitch instead of the reference's multi-node tree:
+  * one flat index space, cut into K pipeline chunks x W rank shards: element i of shard r of chunk k
+    sits at ((k*W + r)*shard + i) in BOTH the flat gradient buffer and the gathered-parameter buffer, so
+    reduce_scatter_tensor / all_gather_into_tensor run zero-copy on contiguous slices (the reference needs
+    a patched c10d with `no_copy=` for that, :370-371) and a parameter has the same offset in both;
+  * one communicator (NVSwitch gives every peer full bandwidth; the reference's 4+ process groups per
+    collective only help on a network with several rails) and one side stream: RS(k+1..) overlaps
+    Adam(k), AG(k) overlaps Adam(k+1..);
+  * gradients are flattened with ONE multi_tensor_scale launch and gathered parameters are scattered
+    back with ONE maybe_cast_mt launch, whatever the number of parameters.
+The kwargs that only steer the reference's process-group fan-out (dwu_num_rs_pg, dwu_num_ar_pg,
+dwu_num_ag_pg, dwu_group_size, num_process_groups, ...) are accepted and ignored.
+"""
+import importlib
+import math
+
+import torch
+import torch.distributed as dist
+
+from ...multi_tensor_apply import multi_tensor_applier
+
+ALIGN = 64          # parameter offsets are multiples of 64 elements (reference :165-173)
+PAD_UNIT = 256      # total length is a multiple of 256*K*W (reference :182-183)
+
+
+def build_layout(numels, world_size, num_chunks):
+    """Offsets of every parameter in the flat space and the chunk/shard geometry.  Pure arithmetic
+    (shared by the optimizer, the tests and the benchmark)."""
+    offsets, off = [], 0
+    for n in numels:
+        offsets.append(off)
+        off = (off + n + ALIGN - 1) // ALIGN * ALIGN
+    unit = PAD_UNIT * num_chunks * world_size
+    total = max(unit, (off + unit - 1) // unit * unit)
+    chunk = total // num_chunks
+    shard = chunk // world_size
+    return {"offsets": offsets, "total": total, "chunk": chunk, "shard": shard,
+            "num_chunks": num_chunks, "world_size": world_size}
+
+
+def shard_fragments(layout, numels, rank):
+    """For every pipeline chunk k: the list of (param index, offset inside the param, offset inside this
+    rank's shard of chunk k, length) where a parameter overlaps the shard (reference :260-301)."""
+    W, shard, chunk = layout["world_size"], layout["shard"], layout["chunk"]
+    out = []
+    for k in range(layout["num_chunks"]):
+        lo = k * chunk + rank * shard
+        hi = lo + shard
+        frags = []
+        for i, (off, n) in enumerate(zip(layout["offsets"], numels)):
+            a, b = max(lo, off), min(hi, off + n)
+            if a < b:
+                frags.append((i, a - off, a - lo, b - a))
+        out.append(frags)
+    return out
+
+
+class DistributedFusedAdam(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, bias_correction=True, betas=(0.9, 0.999), eps=1e-8,
+                 eps_inside_sqrt=False, weight_decay=0., max_grad_norm=0., amsgrad=False, flat_mt=False,
+                 overlap_reductions=True, compute_L2_grad_norm=False, dwu_group_size=0, dwu_num_blocks=4,
+                 dwu_num_chunks=4, dwu_num_rs_pg=1, dwu_num_ar_pg=4, dwu_num_ag_pg=0, predivide=True,
+                 e5m2_allgather=False, do_not_flatten_model=False, step_supports_amp_scaling=True,
+                 num_process_groups=1, current_process_group=None, process_group_id=0, process_group_size=0,
+                 clip_grad_norm=True, model_parallel=False):
+        if amsgrad:
+            raise RuntimeError("DistributedFusedAdam does not support the AMSGrad variant.")
+        if e5m2_allgather:
+            raise NotImplementedError("e5m2-compressed all-gather is outside the hot path (SURVEY.md 8f-4)")
+        super().__init__(params, dict(lr=lr, bias_correction=bias_correction, betas=betas, eps=eps,
+                                      weight_decay=weight_decay, max_grad_norm=max_grad_norm))
+        # kernels are looked up by module name, exactly as the reference does (:78-81)
+        self._dist_adam = importlib.import_module("distributed_adam_cuda")
+        self._contrib = importlib.import_module("fused_adam_cuda")
+        amp_C = importlib.import_module("amp_C")
+        self.multi_tensor_l2norm = amp_C.multi_tensor_l2norm
+        self._multi_tensor_scale = amp_C.multi_tensor_scale
+
+        self.eps_mode = 0 if eps_inside_sqrt else 1
+        self._step_supports_amp_scaling = step_supports_amp_scaling
+        self._predivide = predivide
+        self._compute_L2_grad_norm = compute_L2_grad_norm
+        self._clip_grad_norm = clip_grad_norm
+        self._overlap_reductions = overlap_reductions
+        self._num_chunks_total = max(1, dwu_num_blocks * dwu_num_chunks)   # K pipeline chunks
+        self._global_scale = None
+        self._has_overflow = False
+        self._L2_grad_norm = None
+        self._l2_sq = None
+        self._step = 0
+        self._init_done = False
+        self._resume_state = None
+        self._reduced = False
+
+        self._pg = current_process_group if current_process_group is not None else dist.group.WORLD
+        self._world_size = dist.get_world_size(self._pg)
+        self._rank = dist.get_rank(self._pg)
+
+    # ------------------------------------------------------------------------------------------
+    # lazy construction of the flat buffers (first complete_reductions / step)
+    # ------------------------------------------------------------------------------------------
+    def _init_everything(self):
+        if self._init_done:
+            return
+        self._model_params, self._group_of = [], []
+        for gi, group in enumerate(self.param_groups):
+            for p in group["params"]:
+                if p.requires_grad:
+                    self._model_params.append(p)
+                    self._group_of.append(gi)
+        assert len(self._model_params) > 0, "no parameters to optimise"
+        p0 = self._model_params[0]
+        dev, low = p0.device, p0.dtype
+        assert all(p.dtype == low and p.device == dev for p in self._model_params), \
+            "all parameters must share one dtype and device"
+        self._device, self._low = dev, low
+        self._cuda = dev.type == "cuda"
+        W, K, r = self._world_size, self._num_chunks_total, self._rank
+        numels = [p.numel() for p in self._model_params]
+        L = self._layout = build_layout(numels, W, K)
+        total, chunk, shard = L["total"], L["chunk"], L["shard"]
+
+        self._overflow_buf = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._flat_grads = torch.zeros(total, dtype=low, device=dev)      # RS input  [k][r][shard]
+        self._new_params = torch.zeros(total, dtype=low, device=dev)      # AG output [k][r][shard]
+        self._fp16_g = torch.zeros(K * shard, dtype=low, device=dev)      # RS output, this rank
+        self._fp16_p = torch.zeros(K * shard, dtype=low, device=dev)      # Adam p_copy, AG input
+        self._fp32_p = torch.zeros(K * shard, dtype=torch.float32, device=dev)
+        self._fp32_m = torch.zeros(K * shard, dtype=torch.float32, device=dev)
+        self._fp32_v = torch.zeros(K * shard, dtype=torch.float32, device=dev)
+
+        # views of each parameter's slot in the two full-size buffers
+        self._grad_views = [self._flat_grads[o:o + n].view_as(p) for o, n, p in zip(L["offsets"], numels, self._model_params)]
+        self._param_views = [self._new_params[o:o + n].view_as(p) for o, n, p in zip(L["offsets"], numels, self._model_params)]
+
+        # per-chunk kernel lists over the fragments of this rank's shard + per-fragment hyper-parameters
+        self._chunk_lists, self._chunk_hyper = [], []
+        for k, frags in enumerate(shard_fragments(L, numels, r)):
+            base = k * shard
+            lists = [[], [], [], [], []]
+            b1, b2, bc, ep, wd = [], [], [], [], []
+            for (pi, poff, soff, n) in frags:
+                sl = slice(base + soff, base + soff + n)
+                for lst, buf in zip(lists, (self._fp32_p, self._fp32_m, self._fp32_v, self._fp16_g, self._fp16_p)):
+                    lst.append(buf[sl])
+                g = self.param_groups[self._group_of[pi]]
+                b1.append(g["betas"][0]); b2.append(g["betas"][1]); bc.append(1 if g["bias_correction"] else 0)
+                ep.append(g["eps"]); wd.append(g["weight_decay"])
+            self._chunk_lists.append(lists)
+            self._chunk_hyper.append((torch.tensor(b1, dtype=torch.float32, device=dev),
+                                      torch.tensor(b2, dtype=torch.float32, device=dev),
+                                      torch.tensor(bc, dtype=torch.int32, device=dev),
+                                      torch.tensor(ep, dtype=torch.float32, device=dev),
+                                      torch.tensor(wd, dtype=torch.float32, device=dev)))
+
+        # master weights: this rank's slice of the model parameters (or a loaded checkpoint)
+        if self._resume_state is not None:
+            st = self._resume_state
+            self._step = st["step"]
+            self._fp32_p.copy_(st["fp32_p"]); self._fp32_m.copy_(st["fp32_m"]); self._fp32_v.copy_(st["fp32_v"])
+            self._resume_state = None
+        else:
+            with torch.no_grad():
+                for k, frags in enumerate(shard_fragments(L, numels, r)):
+                    for (pi, poff, soff, n) in frags:
+                        self._fp32_p[k * shard + soff:k * shard + soff + n].copy_(
+                            self._model_params[pi].detach().reshape(-1)[poff:poff + n])
+        if self._cuda:
+            self._comm_stream = torch.cuda.Stream(device=dev)
+            self._rs_done = [torch.cuda.Event() for _ in range(K)]
+            self._adam_done = [torch.cuda.Event() for _ in range(K)]
+        self._init_done = True
+
+    # ------------------------------------------------------------------------------------------
+    # reference API
+    # ------------------------------------------------------------------------------------------
+    def set_global_scale(self, global_scale):
+        """The loss scale the incoming gradients carry; the step kernel divides it out."""
+        self._global_scale = global_scale
+
+    @property
+    def global_scale(self):
+        return self._global_scale
+
+    @property
+    def has_overflow(self):
+        """Overflow seen by strided_check_finite(); reading clears it (reference :509-516)."""
+        has = self._has_overflow
+        self._has_overflow = False
+        return has
+
+    @property
+    def peek_overflow(self):
+        return self._has_overflow
+
+    def strided_check_finite(self, output_params, stride=1, start=-1, end=-1, clear=True):
+        out_p = output_params[start:end] if (0 <= start < end) else output_params
+        self._contrib.strided_check_finite(self._overflow_buf, out_p, stride, 1 if clear else 0)
+        self._has_overflow = self._overflow_buf.item() != 0
+        return self._has_overflow
+
+    @property
+    def L2_grad_norm(self):
+        """Global gradient norm (of the still-scaled, averaged gradients); host value, syncs once."""
+        if not self._compute_L2_grad_norm:
+            return None
+        if self._L2_grad_norm is None and self._l2_sq is not None:
+            self._L2_grad_norm = math.sqrt(float(self._l2_sq.item()))
+        return self._L2_grad_norm
+
+    def _launch_reduce_scatters(self):
+        K, W, shard = self._num_chunks_total, self._world_size, self._layout["shard"]
+        chunk = self._layout["chunk"]
+        for k in range(K):
+            dist.reduce_scatter_tensor(self._fp16_g[k * shard:(k + 1) * shard],
+                                       self._flat_grads[k * chunk:(k + 1) * chunk], group=self._pg)
+            if self._cuda:
+                self._rs_done[k].record(torch.cuda.current_stream(self._device))
+
+    def complete_reductions(self):
+        """Flatten the gradients (predivided by the world size) and start the per-chunk reduce-scatters
+        on the communication stream (reference :552-575)."""
+        self._init_everything()
+        grads, views = [], []
+        for p, v in zip(self._model_params, self._grad_views):
+            if p.grad is None:
+                v.zero_()                       # parameter unused this iteration
+            elif p.grad.data_ptr() != v.data_ptr():
+                grads.append(p.grad); views.append(v)
+        scale = 1.0 / self._world_size if self._predivide else 1.0
+        if grads:
+            multi_tensor_applier(self._multi_tensor_scale, self._overflow_buf, [grads, views], scale)
+        elif scale != 1.0:
+            self._flat_grads.mul_(scale)        # grads were produced directly into the flat buffer
+        if self._cuda:
+            cur = torch.cuda.current_stream(self._device)
+            self._comm_stream.wait_stream(cur)
+            with torch.cuda.stream(self._comm_stream):
+                self._launch_reduce_scatters()
+        else:
+            self._launch_reduce_scatters()
+        self._L2_grad_norm, self._l2_sq = None, None
+        if self._compute_L2_grad_norm:
+            # the shard buffer is contiguous after the reductions: one norm + one scalar all-reduce (:421-441)
+            if self._cuda:
+                torch.cuda.current_stream(self._device).wait_stream(self._comm_stream)
+            n = multi_tensor_applier(self.multi_tensor_l2norm, self._overflow_buf, [[self._fp16_g]], False)[0]
+            self._l2_sq = n * n
+            dist.all_reduce(self._l2_sq, group=self._pg)
+        self._reduced = True
+
+    def _combined_scale(self):
+        """global_scale, enlarged when the (unscaled) gradient norm exceeds max_grad_norm (reference :443-453)."""
+        gs = self._global_scale if self._global_scale is not None else 1.0
+        mx = self.defaults["max_grad_norm"]
+        if self._clip_grad_norm and mx > 0 and self._compute_L2_grad_norm:
+            l2 = self.L2_grad_norm
+            if l2 is not None and math.isfinite(l2):
+                c = mx / (l2 / gs + 1e-6)
+                return gs / min(1, c)
+        return gs
+
+    def _adam_chunk(self, k, combined_scale):
+        lists = self._chunk_lists[k]
+        if len(lists[0]) == 0:
+            return
+        b1, b2, bc, ep, wd = self._chunk_hyper[k]
+        multi_tensor_applier(self._dist_adam.multi_tensor_fused_adam, self._overflow_buf, lists, b1, b2, bc, ep, wd,
+                             self.param_groups[0]["lr"], combined_scale, self._step, self.eps_mode)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = closure() if closure is not None else None
+        if not self._reduced:
+            self.complete_reductions()
+        self._reduced = False
+        K, shard, chunk = self._num_chunks_total, self._layout["shard"], self._layout["chunk"]
+        combined_scale = self._combined_scale()
+        self._step += 1
+        if self._cuda:
+            cur = torch.cuda.current_stream(self._device)
+            for k in range(K):                                  # Adam(k) as soon as RS(k) has landed
+                cur.wait_event(self._rs_done[k])
+                self._adam_chunk(k, combined_scale)
+                self._adam_done[k].record(cur)
+            with torch.cuda.stream(self._comm_stream):          # AG(k) behind Adam(k), on the comm stream
+                for k in range(K):
+                    self._comm_stream.wait_event(self._adam_done[k])
+                    dist.all_gather_into_tensor(self._new_params[k * chunk:(k + 1) * chunk],
+                                                self._fp16_p[k * shard:(k + 1) * shard], group=self._pg)
+            cur.wait_stream(self._comm_stream)
+        else:
+            for k in range(K):
+                self._adam_chunk(k, combined_scale)
+                dist.all_gather_into_tensor(self._new_params[k * chunk:(k + 1) * chunk],
+                                            self._fp16_p[k * shard:(k + 1) * shard], group=self._pg)
+        # gathered parameters -> model parameters, one launch (reference :584-591)
+        multi_tensor_applier(self._contrib.maybe_cast_mt, self._overflow_buf,
+                             [self._param_views, [p.data for p in self._model_params]])
+        return loss
+
+    def state_dict(self):
+        """This rank's shard: {step, fp32_p, fp32_m, fp32_v} (reference :598-616)."""
+        self._init_everything()
+        return {"step": self._step, "fp32_p": self._fp32_p, "fp32_m": self._fp32_m, "fp32_v": self._fp32_v}
+
+    def load_state_dict(self, state_dict):
+        if self._init_done:
+            self._step = state_dict["step"]
+            self._fp32_p.copy_(state_dict["fp32_p"]); self._fp32_m.copy_(state_dict["fp32_m"])
+            self._fp32_v.copy_(state_dict["fp32_v"])
+        else:
+            self._resume_state = state_dict

@@ -44,7 +44,7 @@ const char* dtype_name(int d) {
 
 static void init_tuning() {
   if (g_tile_elems) return;
-  g_tile_elems = 8192;
+  g_tile_elems = 4096;  // swept on B200 (profiles/sweep_tiles_r01.txt): one CTA per 4096-element tile is fastest
   if (const char* e = getenv("B200MT_TILE_ELEMS")) { int v = atoi(e); if (v >= 64) g_tile_elems = v; }
   if (const char* e = getenv("B200MT_GRID_CAP")) { int v = atoi(e); if (v > 0) g_grid_cap = v; }
 }

@@ -1,0 +1,152 @@
+"""CPU, world_size 2 over gloo: the host-side logic of DistributedFusedAdam -- flat layout, shard
+fragments, reduce-scatter / all-gather plumbing, checkpoint shards.  There is no CPU kernel in the
+product, so THIS TEST substitutes the three kernel modules by doubles that call the oracle
+(tests may; the product never does), and checks the sharded result against unsharded AdamW on the
+rank-averaged gradients, as tests/L0/run_optimizers/test_dist_adam.py does on GPUs."""
+import os
+import sys
+import types
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_layout_and_fragments_cover_every_element_once():
+    sys.path.insert(0, os.path.join(ROOT, "rocm-apex_b200"))
+    from apex.contrib.optimizers.distributed_fused_adam import build_layout, shard_fragments
+    numels = [1000, 64, 7, 300000, 1, 65536]
+    for W, K in [(1, 1), (2, 1), (2, 4), (8, 16), (4, 3)]:
+        L = build_layout(numels, W, K)
+        assert L["total"] % (256 * K * W) == 0 and L["chunk"] * K == L["total"] and L["shard"] * W == L["chunk"]
+        assert all(o % 64 == 0 for o in L["offsets"])
+        seen = [torch.zeros(n, dtype=torch.int32) for n in numels]
+        for r in range(W):
+            for k, frags in enumerate(shard_fragments(L, numels, r)):
+                used = 0
+                for (pi, poff, soff, n) in frags:
+                    seen[pi][poff:poff + n] += 1
+                    assert 0 <= soff and soff + n <= L["shard"]
+                    # same element, same flat position
+                    assert L["offsets"][pi] + poff == k * L["chunk"] + r * L["shard"] + soff
+                    used += n
+        assert all(bool((s == 1).all()) for s in seen)
+
+
+def _install_kernel_doubles():
+    from oracle import mt_oracle as O
+
+    def flag_list(t):
+        class F(list):
+            pass
+        f = F([int(t.item())])
+        return f
+
+    amp_c = types.ModuleType("amp_C")
+
+    def multi_tensor_scale(chunk, noop, lists, scale):
+        f = flag_list(noop); O.multi_tensor_scale(f, lists, scale); noop.fill_(f[0])
+
+    def multi_tensor_l2norm(chunk, noop, lists, per_tensor=False):
+        f = flag_list(noop)
+        n, p = O.multi_tensor_l2norm(chunk, f, lists, bool(per_tensor))
+        noop.fill_(f[0])
+        return torch.tensor([float(n)]), (torch.from_numpy(p) if p is not None else torch.empty(0))
+
+    amp_c.multi_tensor_scale, amp_c.multi_tensor_l2norm = multi_tensor_scale, multi_tensor_l2norm
+    dac = types.ModuleType("distributed_adam_cuda")
+
+    def multi_tensor_fused_adam(chunk, noop, lists, b1, b2, bc, eps, wd, lr, grad_scale, step, mode):
+        O.multi_tensor_fused_adam(lists, b1.tolist(), b2.tolist(), bc.tolist(), eps.tolist(), wd.tolist(), lr, grad_scale, step, mode)
+
+    dac.multi_tensor_fused_adam = multi_tensor_fused_adam
+    fac = types.ModuleType("fused_adam_cuda")
+
+    def maybe_cast_mt(chunk, flag, lists):
+        O.maybe_cast_mt([int(flag.item())], lists)
+
+    fac.maybe_cast_mt = maybe_cast_mt
+    sys.modules["amp_C"], sys.modules["distributed_adam_cuda"], sys.modules["fused_adam_cuda"] = amp_c, dac, fac
+
+
+def _worker(rank, world, port, K, dtype_name, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    for p in (os.path.join(ROOT, "rocm-apex_b200"), ROOT):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import apex  # noqa: F401  (real launch shim first, so multi_tensor_applier.available is decided by the real library)
+        _install_kernel_doubles()
+        from apex.contrib.optimizers.distributed_fused_adam import DistributedFusedAdam
+        dtype = getattr(torch, dtype_name)
+        shapes = [(300, 7), (64,), (5,), (1000, 3), (1,)]
+        g0 = torch.Generator().manual_seed(7)
+        init = [torch.randn(s, generator=g0) * 0.1 for s in shapes]
+        params = [torch.nn.Parameter(t.to(dtype)) for t in init]
+        opt = DistributedFusedAdam([{"params": params[:3], "weight_decay": 0.01}, {"params": params[3:], "weight_decay": 0.0}],
+                                   lr=1e-2, betas=(0.9, 0.99), eps=1e-8, dwu_num_blocks=K, dwu_num_chunks=1,
+                                   compute_L2_grad_norm=True, max_grad_norm=0.0, overlap_reductions=False)
+        opt.set_global_scale(8.0)
+        # unsharded reference: AdamW on fp32 masters with the rank-averaged gradient
+        masters = [p.detach().float().clone().requires_grad_() for p in params]
+        ref = torch.optim.AdamW([{"params": masters[:3], "weight_decay": 0.01}, {"params": masters[3:], "weight_decay": 0.0}],
+                                lr=1e-2, betas=(0.9, 0.99), eps=1e-8)
+        for it in range(4):
+            per_rank = []
+            for r in range(world):
+                gr = torch.Generator().manual_seed(100 * it + r)
+                per_rank.append([(torch.randn(s, generator=gr) * 8.0).to(dtype) for s in shapes])
+            for p, g in zip(params, per_rank[rank]):
+                p.grad = g.clone()
+            opt.complete_reductions()
+            # averaged, still-scaled gradient as the reduce-scatter produced it (each term rounded to dtype)
+            avg = [sum((gs[i].float() / world).to(dtype).float() for gs in per_rank).to(dtype).float() for i in range(len(shapes))]
+            want_norm = torch.sqrt(sum((a * a).sum() for a in avg))
+            assert abs(opt.L2_grad_norm - float(want_norm)) <= 1e-3 * float(want_norm)
+            opt.step()
+            for m, a in zip(masters, avg):
+                m.grad = a / 8.0
+            ref.step()
+            tol = 1e-5 if dtype == torch.float32 else 1e-2
+            for p, m in zip(params, masters):
+                assert torch.allclose(p.detach().float(), m.detach().to(dtype).float(), rtol=tol, atol=tol), (it, rank)
+        sd = opt.state_dict()
+        assert sd["step"] == 4 and sd["fp32_p"].numel() == opt._layout["shard"] * K
+        # resume: a fresh optimizer loaded from this rank's shard continues identically
+        params2 = [torch.nn.Parameter(p.detach().clone()) for p in params]
+        opt2 = DistributedFusedAdam([{"params": params2[:3], "weight_decay": 0.01}, {"params": params2[3:], "weight_decay": 0.0}],
+                                    lr=1e-2, betas=(0.9, 0.99), eps=1e-8, dwu_num_blocks=K, dwu_num_chunks=1, overlap_reductions=False)
+        opt2.load_state_dict({k: (v.clone() if torch.is_tensor(v) else v) for k, v in sd.items()})
+        opt2.set_global_scale(8.0)
+        gr = torch.Generator().manual_seed(999 + rank)
+        gnew = [(torch.randn(s, generator=gr) * 8.0).to(dtype) for s in shapes]
+        for p, p2, g in zip(params, params2, gnew):
+            p.grad, p2.grad = g.clone(), g.clone()
+        opt.step(); opt2.step()
+        for p, p2 in zip(params, params2):
+            assert torch.equal(p.detach(), p2.detach())
+        out.put((rank, "ok"))
+    except Exception as e:  # surface the failure to the parent
+        import traceback
+        out.put((rank, "FAIL: " + traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("K,dtype_name", [(1, "bfloat16"), (3, "float32")])
+def test_sharded_adam_matches_unsharded_world2_gloo(K, dtype_name):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29600 + K + (0 if dtype_name == "float32" else 10)
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, K, dtype_name, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in results:
+        assert msg == "ok", "rank %d: %s" % (rank, msg)
