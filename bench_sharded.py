@@ -1,0 +1,239 @@
+"""N > 1 arm of bench.py: BASELINE.json configs[3] -- the ZeRO-style sharded optimizer step of
+DistributedFusedAdam on the Llama-3-8B shape list (291 tensors, 8,030,261,248 params; bf16 gradients and
+model parameters, fp32 master weights and moments sharded over the ranks):
+
+    reduce-scatter(bf16 grads) -> shard-local fused AdamW (one RMW pass, writes the bf16 copy) -> all-gather(bf16 params)
+
+One process per GPU (torch.distributed.run), NCCL over NVLink/NVSwitch.  Strong scaling: the list is fixed,
+each rank owns 1/N of it.  Times are CUDA events on each rank, max over ranks.
+"""
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+import param_shapes
+
+NVLINK_GBS = 770.0     # measured peer-copy bandwidth per direction (B200_PROFILING.md); 900 nominal
+
+
+def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, stream, flat, nparams, shapes, model_name, lib):
+    from bench import peaks, METRIC, UNIT
+    clocks = sampler.stop() if rank == 0 else None
+    host = torch.empty(1 << 27, dtype=torch.bfloat16).pin_memory()
+    host.normal_(0, 1)
+    e2e_steps = max(2, min(args.steps, 5))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def e2e_step():
+        for off in range(0, flat.numel(), host.numel()):
+            n = min(host.numel(), flat.numel() - off)
+            flat[off:off + n].copy_(host[:n], non_blocking=True)
+        opt.complete_reductions()
+        opt.step()
+        return float(opt._new_params[0])
+
+    e2e_step()
+    torch.cuda.synchronize(); dist.barrier()
+    e0.record(stream)
+    for _ in range(e2e_steps):
+        e2e_step()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    e2e_ms = e0.elapsed_time(e1) / e2e_steps
+    t = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    tl = torch.tensor([float(launches)], device=dev, dtype=torch.float64)
+    dist.all_reduce(tl, op=dist.ReduceOp.SUM)
+    ms, e2e_ms = t.tolist()
+    if rank == 0:
+        peak, peak_src = peaks()
+        total = opt._layout["total"]
+        shard_elems = opt._layout["shard"]
+        # per GPU and direction: out = my whole gradient buffer pulled by the switch (2*total) + my shard's
+        # parameters sent once (2*shard); in = my shard's reduced gradients (2*shard) + everybody's parameters (2*total)
+        nv_bytes = 2.0 * total + 2.0 * shard_elems
+        kbytes = 28.0 * shard_elems
+        achieved = kbytes / (ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": nparams / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "configs[3]: DistributedFusedAdam sharded step on the %s shape list as ONE kernel over NVSwitch multicast: "
+                                   "bf16 grads reduced in the switch on load (multimem.ld_reduce), fused AdamW (fp32 master/moments), "
+                                   "bf16 params broadcast by the switch on store (multimem.st)" % model_name,
+                       "tensors": len(shapes), "params": nparams, "flat_elems": total, "parallelism": "zero-dp%d" % world,
+                       "l2": "inputs larger than L2 (%.1f GB of optimizer state per rank)" % (12.0 * shard_elems / 1e9)},
+            "roofline": {"bound": "nvlink", "achieved": nv_bytes / (ms * 1e-3) / 1e9, "peak": NVLINK_GBS, "unit": "GB/s",
+                         "frac": nv_bytes / (ms * 1e-3) / 1e9 / NVLINK_GBS, "traffic": None,
+                         "kernel": "mt_stream_kernel<DistAdamOp<mc_bf16,true>> (includes both barriers)",
+                         "bytes_per_launch": nv_bytes, "avg_launch_ms": ms,
+                         "peak_source": "measured peer-copy bandwidth per direction (B200_PROFILING.md), 900 nominal",
+                         "hbm_gbs_of_shard_kernel": achieved, "hbm_frac": achieved / peak},
+            "cpu_baseline": None,
+            "e2e": {"value": nparams / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 2 * total * world, "d2h_bytes_per_step": 2 * world,
+                    "ms_per_step": e2e_ms, "steps": e2e_steps,
+                    "api": "DistributedFusedAdam(fused_collectives=True).complete_reductions() + step(), grads copied from pinned host each step"},
+            "gpu_launches": int(tl.item()),
+            "clocks": clocks,
+        }
+        print(json.dumps(line))
+    dist.destroy_process_group()
+
+
+def run_sharded(args):
+    from bench import ClockSampler, peaks, METRIC, UNIT, ROOT
+    from apex.contrib.optimizers import DistributedFusedAdam
+    import _b200mt as mt
+
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    model_name = os.environ.get("B200MT_SHARDED_MODEL", "llama3_8b")
+    K = int(os.environ.get("B200MT_SHARDED_CHUNKS", "8"))
+    fused = os.environ.get("B200MT_SHARDED_FUSED", "0") == "1"   # one multimem kernel instead of RS -> Adam -> AG
+    if fused:
+        K = 1
+    shapes = param_shapes.MODELS[model_name]()
+    nparams = param_shapes.numel(shapes)
+
+    # model parameters (bf16).  They are created as views of one flat allocation only to keep set-up fast;
+    # the optimizer re-points them into its all-gather buffer (zero_copy_params) anyway.
+    gen = torch.Generator(device=dev).manual_seed(1)
+    params = []
+    for s in shapes:
+        params.append(torch.nn.Parameter((torch.randn(s, generator=gen, device=dev, dtype=torch.float32) * 0.02).to(torch.bfloat16)))
+    opt = DistributedFusedAdam(params, lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1, dwu_num_blocks=K,
+                               dwu_num_chunks=1, predivide=False, overlap_reductions=False, zero_copy_params=True,
+                               fused_collectives=fused)
+    opt.set_global_scale(float(world))          # gradients are summed by the reduce-scatter; the kernel divides by W
+    flat = opt.attach_flat_grads()
+    ggen = torch.Generator(device=dev).manual_seed(100 + rank)
+    piece = 1 << 26
+    for off in range(0, flat.numel(), piece):   # randn(seed = rank) in pieces (fp32 staging)
+        n = min(piece, flat.numel() - off)
+        flat[off:off + n].copy_(torch.randn(n, generator=ggen, device=dev))
+    torch.cuda.synchronize()
+    lib = mt.lib
+
+    def step():
+        opt.complete_reductions()
+        opt.step()
+
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
+        step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    stream = torch.cuda.current_stream(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = lib.b200mt_launch_count()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    launches = lib.b200mt_launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+
+    shard_elems = opt._layout["shard"] * K
+    if fused:
+        return _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, stream, flat, nparams, shapes, model_name, lib)
+    # shard kernel alone (no collectives): the roofline of the dominant kernel on this rank
+    ks = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    kreps = 5
+    torch.cuda.synchronize()
+    ks[0].record(stream)
+    for _ in range(kreps):
+        for k in range(K):
+            opt._adam_chunk(k, float(world))
+    ks[1].record(stream)
+    torch.cuda.synchronize()
+    kernel_ms = ks[0].elapsed_time(ks[1]) / kreps
+
+    # collectives alone
+    cs = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    chunk, shard = opt._layout["chunk"], opt._layout["shard"]
+    torch.cuda.synchronize(); dist.barrier()
+    cs[0].record(stream)
+    for k in range(K):
+        dist.reduce_scatter_tensor(opt._fp16_g[k * shard:(k + 1) * shard], opt._flat_grads[k * chunk:(k + 1) * chunk])
+    cs[1].record(stream)
+    for k in range(K):
+        dist.all_gather_into_tensor(opt._new_params[k * chunk:(k + 1) * chunk], opt._fp16_p[k * shard:(k + 1) * shard])
+    cs[2].record(stream)
+    torch.cuda.synchronize()
+    rs_ms, ag_ms = cs[0].elapsed_time(cs[1]), cs[1].elapsed_time(cs[2])
+
+    # e2e: the step's gradients arrive from pinned host memory (a 256 MiB pinned window copied repeatedly to
+    # fill the flat buffer: pinning 16 GB per rank is not reasonable), the result read back is the gradient norm
+    host = torch.empty(1 << 27, dtype=torch.bfloat16).pin_memory()
+    host.normal_(0, 1)
+    e2e_steps = max(2, min(args.steps, 5))
+
+    def e2e_step():
+        for off in range(0, flat.numel(), host.numel()):
+            n = min(host.numel(), flat.numel() - off)
+            flat[off:off + n].copy_(host[:n], non_blocking=True)
+        opt.complete_reductions()
+        opt.step()
+        return float(opt._fp16_p[0])     # D2H read of one updated parameter: forces completion of the step
+
+    e2e_step()
+    torch.cuda.synchronize(); dist.barrier()
+    e0.record(stream)
+    for _ in range(e2e_steps):
+        e2e_step()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    e2e_ms = e0.elapsed_time(e1) / e2e_steps
+
+    t = torch.tensor([ms, kernel_ms, rs_ms, ag_ms, e2e_ms], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    tl = torch.tensor([float(launches)], device=dev, dtype=torch.float64)
+    dist.all_reduce(tl, op=dist.ReduceOp.SUM)
+    ms, kernel_ms, rs_ms, ag_ms, e2e_ms = t.tolist()
+    if rank == 0:
+        peak, peak_src = peaks()
+        total = opt._layout["total"]
+        kbytes = 28.0 * shard_elems
+        achieved = kbytes / (kernel_ms * 1e-3) / 1e9
+        nv_bytes = 2.0 * total * (world - 1) / world            # per direction per GPU, for each of RS and AG
+        line = {
+            "metric": METRIC, "value": nparams / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "configs[3]: DistributedFusedAdam sharded step on the %s shape list: bf16 grad reduce-scatter -> "
+                                   "shard-local fused AdamW (fp32 master/moments, bf16 copy) -> bf16 param all-gather, NCCL" % model_name,
+                       "tensors": len(shapes), "params": nparams, "flat_elems": total, "pipeline_chunks": K,
+                       "parallelism": "zero-dp%d" % world,
+                       "l2": "inputs larger than L2 (%.1f GB of optimizer state per rank)" % (12.0 * shard_elems / 1e9)},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "kernel": "mt_stream_kernel<DistAdamOp<__nv_bfloat16,true>>", "bytes_per_launch": kbytes / K,
+                         "avg_launch_ms": kernel_ms / K, "peak_source": peak_src},
+            "nvlink": {"bytes_per_direction_per_gpu_per_collective": nv_bytes, "reduce_scatter_ms": rs_ms, "all_gather_ms": ag_ms,
+                       "reduce_scatter_gbs": nv_bytes / (rs_ms * 1e-3) / 1e9, "all_gather_gbs": nv_bytes / (ag_ms * 1e-3) / 1e9,
+                       "peak_gbs": NVLINK_GBS, "frac_rs": nv_bytes / (rs_ms * 1e-3) / 1e9 / NVLINK_GBS,
+                       "frac_ag": nv_bytes / (ag_ms * 1e-3) / 1e9 / NVLINK_GBS,
+                       "step_floor_ms": 2 * nv_bytes / (NVLINK_GBS * 1e9) * 1e3,
+                       "overlap_efficiency": (rs_ms + ag_ms) / ms, "shard_kernel_ms": kernel_ms},
+            "cpu_baseline": None,
+            "e2e": {"value": nparams / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 2 * total * world, "d2h_bytes_per_step": 2 * world,
+                    "ms_per_step": e2e_ms, "steps": e2e_steps,
+                    "api": "DistributedFusedAdam.complete_reductions() + step(), grads copied from pinned host each step"},
+            "gpu_launches": int(tl.item()),
+            "clocks": clocks,
+        }
+        print(json.dumps(line))
+    dist.destroy_process_group()

@@ -142,6 +142,22 @@ int b200mt_dist_adam(const b200mt_lists* lists, int chunk_size, int32_t* noop,
                      const float* per_tensor_weight_decay, float lr, float grad_scale, int step,
                      int mode, void* stream);
 
+/* ---- b200mt_dist_adam_nvls -- the sharded step of DistributedFusedAdam as ONE kernel (extension; it
+ * replaces the reference's three-step sequence reduce_scatter -> multi_tensor_fused_adam -> all_gather,
+ * apex/contrib/optimizers/distributed_fused_adam.py:409,443-467,477).
+ * lists = [p32, m32, v32, g_mc, p_copy_mc]: lists 3 and 4 hold addresses inside CUDA multicast objects
+ * (NVLS) bound to the same symmetric buffers on every GPU of the NVSwitch domain, at this rank's shard.
+ * The gradient load is multimem.ld_reduce (summed over all ranks inside the switch, fp32 accumulation),
+ * the parameter store is multimem.st (replicated to all ranks by the switch): no separate collective.
+ * dtype[3] == dtype[4] in {B200MT_F16, B200MT_BF16}; every fragment must be a multiple of 4 elements,
+ * 8-byte (lists 3,4) / 16-byte (lists 0-2) aligned.  The caller brackets the launch with cross-GPU
+ * barriers (all ranks' gradients written before; all ranks' kernels finished after). */
+int b200mt_dist_adam_nvls(const b200mt_lists* lists, int chunk_size, int32_t* noop,
+                          const float* per_tensor_beta1, const float* per_tensor_beta2,
+                          const int32_t* per_tensor_bias_correction, const float* per_tensor_eps,
+                          const float* per_tensor_weight_decay, float lr, float grad_scale, int step,
+                          int mode, void* stream);
+
 /* ---- fused_adam_cuda.adam_mt / maybe_cast_mt / strided_check_finite
  *      (apex/contrib/csrc/optimizers/fused_adam_cuda_kernel.cu:283-387, :939-960, :785-812)
  * adam_mt lists = [p, m, v, g] or [p, m, v, g, p_copy]; step_size form (eps not rescaled). */

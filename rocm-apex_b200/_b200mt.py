@@ -14,7 +14,9 @@ import numpy as np
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "libb200mt.so")
+# B200MT_LIB: load another build of the same library (tuning experiments with different compile-time
+# vector widths); the default is the in-tree build next to this file.
+_LIB_PATH = os.environ.get("B200MT_LIB") or os.path.join(_HERE, "libb200mt.so")
 
 F32, F16, BF16, F64, U8 = 0, 1, 2, 3, 4
 MAX_DEPTH = 5
@@ -71,6 +73,7 @@ def _load():
         "b200mt_lamb_stage1": (c_int, [LP, c_int, vp, vp, c_int, c_float, c_float, c_float, c_float, vp]),
         "b200mt_lamb_stage2": (c_int, [LP, c_int, vp, vp, vp, c_float, c_float, c_int, vp]),
         "b200mt_dist_adam": (c_int, [LP, c_int, vp, vp, vp, vp, vp, vp, c_float, c_float, c_int, c_int, vp]),
+        "b200mt_dist_adam_nvls": (c_int, [LP, c_int, vp, vp, vp, vp, vp, vp, c_float, c_float, c_int, c_int, vp]),
         "b200mt_contrib_adam": (c_int, [LP, c_int, vp, c_float, c_float, c_float, c_float, c_float, c_int,
                                         c_int, c_int, c_float, vp]),
         "b200mt_maybe_cast": (c_int, [LP, c_int, vp, vp]),
@@ -98,6 +101,27 @@ def dtype_code(t):
         return _DTYPE_CODE[t.dtype]
     except KeyError:
         raise RuntimeError("multi_tensor_apply not implemented for '%s'" % str(t.dtype).replace("torch.", ""))
+
+
+class RawBuffer(object):
+    """A device address range that is not a torch tensor -- e.g. an address inside a CUDA multicast
+    object, which no tensor may alias.  Quacks enough like a tensor for pack()."""
+    is_sparse = False
+
+    def __init__(self, ptr, numel, dtype, device):
+        self._ptr, self._numel, self.dtype, self.device = int(ptr), int(numel), dtype, device
+
+    def data_ptr(self):
+        return self._ptr
+
+    def numel(self):
+        return self._numel
+
+    def dim(self):
+        return 1
+
+    def is_contiguous(self, memory_format=None):
+        return True
 
 
 class Packed(object):

@@ -73,7 +73,17 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                  dwu_num_chunks=4, dwu_num_rs_pg=1, dwu_num_ar_pg=4, dwu_num_ag_pg=0, predivide=True,
                  e5m2_allgather=False, do_not_flatten_model=False, step_supports_amp_scaling=True,
                  num_process_groups=1, current_process_group=None, process_group_id=0, process_group_size=0,
-                 clip_grad_norm=True, model_parallel=False):
+                 clip_grad_norm=True, model_parallel=False, zero_copy_params=False, fused_collectives=False):
+        # fused_collectives (not in the reference): the flat gradient and gathered-parameter buffers are
+        # symmetric-memory allocations bound to NVSwitch multicast objects, and the whole step is ONE kernel:
+        # gradients are summed over the ranks inside the switch while they are loaded (multimem.ld_reduce) and
+        # the updated low-precision parameters are replicated to every rank by the switch as they are stored
+        # (multimem.st).  No reduce_scatter, no all_gather, no pipeline chunks; two cross-GPU barriers per step.
+        self._fused = fused_collectives
+        # zero_copy_params (not in the reference): re-point every model parameter's storage at its slot of
+        # the all-gather output buffer, so the gathered parameters ARE the model parameters and the final
+        # scatter-back pass (maybe_cast_mt, 4 B/param of HBM traffic) disappears.
+        self._zero_copy_params = zero_copy_params
         if amsgrad:
             raise RuntimeError("DistributedFusedAdam does not support the AMSGrad variant.")
         if e5m2_allgather:
@@ -94,6 +104,11 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         self._clip_grad_norm = clip_grad_norm
         self._overlap_reductions = overlap_reductions
         self._num_chunks_total = max(1, dwu_num_blocks * dwu_num_chunks)   # K pipeline chunks
+        if self._fused:
+            self._num_chunks_total = 1          # one kernel, nothing to pipeline
+            if compute_L2_grad_norm:
+                raise NotImplementedError("fused_collectives never materialises the reduced gradients; "
+                                          "compute the gradient norm before the step instead")
         self._global_scale = None
         self._has_overflow = False
         self._L2_grad_norm = None
@@ -132,10 +147,23 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         total, chunk, shard = L["total"], L["chunk"], L["shard"]
 
         self._overflow_buf = torch.zeros(1, dtype=torch.int32, device=dev)
-        self._flat_grads = torch.zeros(total, dtype=low, device=dev)      # RS input  [k][r][shard]
-        self._new_params = torch.zeros(total, dtype=low, device=dev)      # AG output [k][r][shard]
-        self._fp16_g = torch.zeros(K * shard, dtype=low, device=dev)      # RS output, this rank
-        self._fp16_p = torch.zeros(K * shard, dtype=low, device=dev)      # Adam p_copy, AG input
+        if self._fused:
+            import torch.distributed._symmetric_memory as symm_mem
+            assert self._cuda, "fused_collectives needs CUDA devices on one NVSwitch domain"
+            self._flat_grads = symm_mem.empty(total, dtype=low, device=dev)
+            self._new_params = symm_mem.empty(total, dtype=low, device=dev)
+            self._flat_grads.zero_(); self._new_params.zero_()
+            self._hdl_g = symm_mem.rendezvous(self._flat_grads, self._pg.group_name)
+            self._hdl_p = symm_mem.rendezvous(self._new_params, self._pg.group_name)
+            if not (self._hdl_g.multicast_ptr and self._hdl_p.multicast_ptr):
+                raise RuntimeError("fused_collectives: no multicast (NVLS) address for the symmetric buffers; "
+                                   "this needs an NVSwitch domain with multicast support")
+        else:
+            self._flat_grads = torch.zeros(total, dtype=low, device=dev)      # RS input  [k][r][shard]
+            self._new_params = torch.zeros(total, dtype=low, device=dev)      # AG output [k][r][shard]
+        nlow = 0 if self._fused else K * shard                            # not materialised when fused
+        self._fp16_g = torch.zeros(nlow, dtype=low, device=dev)           # RS output, this rank
+        self._fp16_p = torch.zeros(nlow, dtype=low, device=dev)           # Adam p_copy, AG input
         self._fp32_p = torch.zeros(K * shard, dtype=torch.float32, device=dev)
         self._fp32_m = torch.zeros(K * shard, dtype=torch.float32, device=dev)
         self._fp32_v = torch.zeros(K * shard, dtype=torch.float32, device=dev)
@@ -151,9 +179,22 @@ class DistributedFusedAdam(torch.optim.Optimizer):
             lists = [[], [], [], [], []]
             b1, b2, bc, ep, wd = [], [], [], [], []
             for (pi, poff, soff, n) in frags:
-                sl = slice(base + soff, base + soff + n)
-                for lst, buf in zip(lists, (self._fp32_p, self._fp32_m, self._fp32_v, self._fp16_g, self._fp16_p)):
-                    lst.append(buf[sl])
+                if self._fused:
+                    # multicast accesses are whole 16-byte vectors of 8 elements: extend the fragment into the (zero, unowned)
+                    # alignment padding that follows every parameter; g and p_copy are multicast addresses of
+                    # this fragment's position in the flat space
+                    from _b200mt import RawBuffer
+                    n = (n + 7) // 8 * 8
+                    flat_pos = k * chunk + r * shard + soff
+                    esize = self._flat_grads.element_size()
+                    for lst, buf in zip(lists[:3], (self._fp32_p, self._fp32_m, self._fp32_v)):
+                        lst.append(buf[base + soff:base + soff + n])
+                    lists[3].append(RawBuffer(self._hdl_g.multicast_ptr + flat_pos * esize, n, low, dev))
+                    lists[4].append(RawBuffer(self._hdl_p.multicast_ptr + flat_pos * esize, n, low, dev))
+                else:
+                    sl = slice(base + soff, base + soff + n)
+                    for lst, buf in zip(lists, (self._fp32_p, self._fp32_m, self._fp32_v, self._fp16_g, self._fp16_p)):
+                        lst.append(buf[sl])
                 g = self.param_groups[self._group_of[pi]]
                 b1.append(g["betas"][0]); b2.append(g["betas"][1]); bc.append(1 if g["bias_correction"] else 0)
                 ep.append(g["eps"]); wd.append(g["weight_decay"])
@@ -176,6 +217,11 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                     for (pi, poff, soff, n) in frags:
                         self._fp32_p[k * shard + soff:k * shard + soff + n].copy_(
                             self._model_params[pi].detach().reshape(-1)[poff:poff + n])
+        if self._zero_copy_params:
+            with torch.no_grad():
+                for p, v in zip(self._model_params, self._param_views):
+                    v.copy_(p.detach())
+                    p.data = v
         if self._cuda:
             self._comm_stream = torch.cuda.Stream(device=dev)
             self._rs_done = [torch.cuda.Event() for _ in range(K)]
@@ -219,6 +265,15 @@ class DistributedFusedAdam(torch.optim.Optimizer):
             self._L2_grad_norm = math.sqrt(float(self._l2_sq.item()))
         return self._L2_grad_norm
 
+    def attach_flat_grads(self):
+        """Points every parameter's .grad at its slot of the flat gradient buffer, so that backward
+        accumulates straight into the reduce-scatter input and complete_reductions() has nothing to
+        flatten (the reference keeps such views in _individual_flat_grads, :209-211)."""
+        self._init_everything()
+        for p, v in zip(self._model_params, self._grad_views):
+            p.grad = v
+        return self._flat_grads
+
     def _launch_reduce_scatters(self):
         K, W, shard = self._num_chunks_total, self._world_size, self._layout["shard"]
         chunk = self._layout["chunk"]
@@ -243,7 +298,9 @@ class DistributedFusedAdam(torch.optim.Optimizer):
             multi_tensor_applier(self._multi_tensor_scale, self._overflow_buf, [grads, views], scale)
         elif scale != 1.0:
             self._flat_grads.mul_(scale)        # grads were produced directly into the flat buffer
-        if self._cuda:
+        if self._fused:
+            pass                                # the reduction happens inside the step kernel
+        elif self._cuda:
             cur = torch.cuda.current_stream(self._device)
             self._comm_stream.wait_stream(cur)
             with torch.cuda.stream(self._comm_stream):
@@ -276,7 +333,8 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         if len(lists[0]) == 0:
             return
         b1, b2, bc, ep, wd = self._chunk_hyper[k]
-        multi_tensor_applier(self._dist_adam.multi_tensor_fused_adam, self._overflow_buf, lists, b1, b2, bc, ep, wd,
+        op = self._dist_adam.multi_tensor_fused_adam_nvls if self._fused else self._dist_adam.multi_tensor_fused_adam
+        multi_tensor_applier(op, self._overflow_buf, lists, b1, b2, bc, ep, wd,
                              self.param_groups[0]["lr"], combined_scale, self._step, self.eps_mode)
 
     @torch.no_grad()
@@ -288,7 +346,12 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         K, shard, chunk = self._num_chunks_total, self._layout["shard"], self._layout["chunk"]
         combined_scale = self._combined_scale()
         self._step += 1
-        if self._cuda:
+        if self._fused:
+            self._hdl_g.barrier(channel=0)      # every rank's gradients are in its flat buffer
+            self._adam_chunk(0, combined_scale) # load = in-switch reduce, store = in-switch broadcast
+            self._hdl_p.barrier(channel=1)      # every rank's kernel is done: parameters complete everywhere,
+                                                # and nobody is still reading this rank's gradients
+        elif self._cuda:
             cur = torch.cuda.current_stream(self._device)
             for k in range(K):                                  # Adam(k) as soon as RS(k) has landed
                 cur.wait_event(self._rs_done[k])
@@ -305,9 +368,10 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                 self._adam_chunk(k, combined_scale)
                 dist.all_gather_into_tensor(self._new_params[k * chunk:(k + 1) * chunk],
                                             self._fp16_p[k * shard:(k + 1) * shard], group=self._pg)
-        # gathered parameters -> model parameters, one launch (reference :584-591)
-        multi_tensor_applier(self._contrib.maybe_cast_mt, self._overflow_buf,
-                             [self._param_views, [p.data for p in self._model_params]])
+        if not self._zero_copy_params:
+            # gathered parameters -> model parameters, one launch (reference :584-591)
+            multi_tensor_applier(self._contrib.maybe_cast_mt, self._overflow_buf,
+                                 [self._param_views, [p.data for p in self._model_params]])
         return loss
 
     def state_dict(self):

@@ -115,6 +115,44 @@ __device__ __forceinline__ void st_u2(uint2* p, uint2 v) {
 #endif
 }
 
+// 256-bit global accesses (sm_100+: LDG.E.256 / STG.E.256), 32-byte aligned
+__device__ __forceinline__ void ld_f8(const void* p, float (&r)[8]) {
+  asm volatile("ld.global.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]), "=f"(r[4]), "=f"(r[5]), "=f"(r[6]), "=f"(r[7])
+               : "l"(p) : "memory");
+}
+__device__ __forceinline__ void st_f8(void* p, const float (&r)[8]) {
+  asm volatile("st.global.L1::no_allocate.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               :: "l"(p), "f"(r[0]), "f"(r[1]), "f"(r[2]), "f"(r[3]), "f"(r[4]), "f"(r[5]), "f"(r[6]), "f"(r[7])
+               : "memory");
+}
+__device__ __forceinline__ uint4 ld_u4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void st_u4(void* p, uint4 v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void bf16x2_to_f(unsigned v, float& lo, float& hi) {
+  lo = __uint_as_float(v << 16); hi = __uint_as_float(v & 0xffff0000u);
+}
+__device__ __forceinline__ unsigned f_to_bf16x2(float lo, float hi) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<unsigned*>(&a);
+}
+__device__ __forceinline__ void f16x2_to_f(unsigned v, float& lo, float& hi) {
+  float2 a = __half22float2(*reinterpret_cast<__half2*>(&v)); lo = a.x; hi = a.y;
+}
+__device__ __forceinline__ unsigned f_to_f16x2(float lo, float hi) {
+  __half2 a = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<unsigned*>(&a);
+}
+
+// Elem<T>: SIZE bytes per element; VECTORISED types are accessed as vectors of V = 4 or 8 elements
+// (V*SIZE bytes, aligned to that), the others element by element.
 template <typename T> struct Elem;
 
 template <> struct Elem<float> {
@@ -126,6 +164,8 @@ template <> struct Elem<float> {
   static __device__ __forceinline__ void st4(void* p, const float (&r)[4]) {
     st_f4(reinterpret_cast<float4*>(p), make_float4(r[0], r[1], r[2], r[3]));
   }
+  static __device__ __forceinline__ void ld8(const void* p, float (&r)[8]) { ld_f8(p, r); }
+  static __device__ __forceinline__ void st8(void* p, const float (&r)[8]) { st_f8(p, r); }
   static __device__ __forceinline__ float ld1(const void* p) { return *reinterpret_cast<const float*>(p); }
   static __device__ __forceinline__ void st1(void* p, float v) { *reinterpret_cast<float*>(p) = v; }
   static __device__ __forceinline__ float round_trip(float v) { return v; }
@@ -146,6 +186,13 @@ template <> struct Elem<__half> {
     v.x = *reinterpret_cast<unsigned*>(&a);
     v.y = *reinterpret_cast<unsigned*>(&b);
     st_u2(reinterpret_cast<uint2*>(p), v);
+  }
+  static __device__ __forceinline__ void ld8(const void* p, float (&r)[8]) {
+    uint4 v = ld_u4(p);
+    f16x2_to_f(v.x, r[0], r[1]); f16x2_to_f(v.y, r[2], r[3]); f16x2_to_f(v.z, r[4], r[5]); f16x2_to_f(v.w, r[6], r[7]);
+  }
+  static __device__ __forceinline__ void st8(void* p, const float (&r)[8]) {
+    st_u4(p, make_uint4(f_to_f16x2(r[0], r[1]), f_to_f16x2(r[2], r[3]), f_to_f16x2(r[4], r[5]), f_to_f16x2(r[6], r[7])));
   }
   static __device__ __forceinline__ float ld1(const void* p) { return __half2float(*reinterpret_cast<const __half*>(p)); }
   static __device__ __forceinline__ void st1(void* p, float v) { *reinterpret_cast<__half*>(p) = __float2half_rn(v); }
@@ -168,6 +215,13 @@ template <> struct Elem<__nv_bfloat16> {
     v.y = *reinterpret_cast<unsigned*>(&b);
     st_u2(reinterpret_cast<uint2*>(p), v);
   }
+  static __device__ __forceinline__ void ld8(const void* p, float (&r)[8]) {
+    uint4 v = ld_u4(p);
+    bf16x2_to_f(v.x, r[0], r[1]); bf16x2_to_f(v.y, r[2], r[3]); bf16x2_to_f(v.z, r[4], r[5]); bf16x2_to_f(v.w, r[6], r[7]);
+  }
+  static __device__ __forceinline__ void st8(void* p, const float (&r)[8]) {
+    st_u4(p, make_uint4(f_to_bf16x2(r[0], r[1]), f_to_bf16x2(r[2], r[3]), f_to_bf16x2(r[4], r[5]), f_to_bf16x2(r[6], r[7])));
+  }
   static __device__ __forceinline__ float ld1(const void* p) { return __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(p)); }
   static __device__ __forceinline__ void st1(void* p, float v) { *reinterpret_cast<__nv_bfloat16*>(p) = __float2bfloat16_rn(v); }
   static __device__ __forceinline__ float round_trip(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
@@ -187,10 +241,108 @@ template <> struct Elem<double> {
 #pragma unroll
     for (int i = 0; i < 4; i++) d[i] = (double)r[i];
   }
+  static __device__ __forceinline__ void ld8(const void* p, float (&r)[8]) {
+    const double* d = reinterpret_cast<const double*>(p);
+#pragma unroll
+    for (int i = 0; i < 8; i++) r[i] = (float)d[i];
+  }
+  static __device__ __forceinline__ void st8(void* p, const float (&r)[8]) {
+    double* d = reinterpret_cast<double*>(p);
+#pragma unroll
+    for (int i = 0; i < 8; i++) d[i] = (double)r[i];
+  }
   static __device__ __forceinline__ float ld1(const void* p) { return (float)*reinterpret_cast<const double*>(p); }
   static __device__ __forceinline__ void st1(void* p, float v) { *reinterpret_cast<double*>(p) = (double)v; }
   static __device__ __forceinline__ float round_trip(float v) { return v; }
 };
+
+// Multicast (NVLS) views of 16-bit lists, for the fused compute+collective kernels.  The pointer is
+// an address inside a CUDA multicast object bound to the same symmetric buffer on every GPU of the
+// NVSwitch domain:
+//   ld4 = multimem.ld_reduce.add : the switch fetches the 8 bytes from EVERY GPU and returns their sum
+//         (accumulated in fp32) -- the reduce-scatter happens inside the gradient load;
+//   st4 = multimem.st            : one store, replicated by the switch into every GPU's buffer --
+//         the all-gather happens inside the parameter write.
+// Only whole, 8-byte aligned quads exist in this address space (the host entry point enforces it),
+// so the scalar accessors must never run.
+struct mc_bf16 {};
+struct mc_f16 {};
+
+template <> struct Elem<mc_bf16> {
+  static constexpr int SIZE = 2, QUAD_ALIGN = 8;
+  static __device__ __forceinline__ void ld4(const void* p, float (&r)[4]) {
+    unsigned x, y;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v2.bf16x2 {%0,%1}, [%2];"
+                 : "=r"(x), "=r"(y) : "l"(p) : "memory");
+    r[0] = __uint_as_float(x << 16); r[1] = __uint_as_float(x & 0xffff0000u);
+    r[2] = __uint_as_float(y << 16); r[3] = __uint_as_float(y & 0xffff0000u);
+  }
+  static __device__ __forceinline__ void st4(void* p, const float (&r)[4]) {
+    __nv_bfloat162 a = __floats2bfloat162_rn(r[0], r[1]);
+    __nv_bfloat162 b = __floats2bfloat162_rn(r[2], r[3]);
+    asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};"
+                 :: "l"(p), "r"(*reinterpret_cast<unsigned*>(&a)), "r"(*reinterpret_cast<unsigned*>(&b)) : "memory");
+  }
+  static __device__ __forceinline__ void ld8(const void* p, float (&r)[8]) {
+    unsigned x, y, z, w;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(x), "=r"(y), "=r"(z), "=r"(w) : "l"(p) : "memory");
+    bf16x2_to_f(x, r[0], r[1]); bf16x2_to_f(y, r[2], r[3]); bf16x2_to_f(z, r[4], r[5]); bf16x2_to_f(w, r[6], r[7]);
+  }
+  static __device__ __forceinline__ void st8(void* p, const float (&r)[8]) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "r"(f_to_bf16x2(r[0], r[1])), "r"(f_to_bf16x2(r[2], r[3])), "r"(f_to_bf16x2(r[4], r[5])),
+                    "r"(f_to_bf16x2(r[6], r[7])) : "memory");
+  }
+  static __device__ __forceinline__ float ld1(const void*) { __trap(); return 0.f; }
+  static __device__ __forceinline__ void st1(void*, float) { __trap(); }
+  static __device__ __forceinline__ float round_trip(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+};
+
+template <> struct Elem<mc_f16> {
+  static constexpr int SIZE = 2, QUAD_ALIGN = 8;
+  static __device__ __forceinline__ void ld4(const void* p, float (&r)[4]) {
+    unsigned x, y;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v2.f16x2 {%0,%1}, [%2];"
+                 : "=r"(x), "=r"(y) : "l"(p) : "memory");
+    float2 a = __half22float2(*reinterpret_cast<__half2*>(&x));
+    float2 b = __half22float2(*reinterpret_cast<__half2*>(&y));
+    r[0] = a.x; r[1] = a.y; r[2] = b.x; r[3] = b.y;
+  }
+  static __device__ __forceinline__ void st4(void* p, const float (&r)[4]) {
+    __half2 a = __floats2half2_rn(r[0], r[1]);
+    __half2 b = __floats2half2_rn(r[2], r[3]);
+    asm volatile("multimem.st.relaxed.sys.global.v2.f16x2 [%0], {%1,%2};"
+                 :: "l"(p), "r"(*reinterpret_cast<unsigned*>(&a)), "r"(*reinterpret_cast<unsigned*>(&b)) : "memory");
+  }
+  static __device__ __forceinline__ void ld8(const void* p, float (&r)[8]) {
+    unsigned x, y, z, w;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(x), "=r"(y), "=r"(z), "=r"(w) : "l"(p) : "memory");
+    f16x2_to_f(x, r[0], r[1]); f16x2_to_f(y, r[2], r[3]); f16x2_to_f(z, r[4], r[5]); f16x2_to_f(w, r[6], r[7]);
+  }
+  static __device__ __forceinline__ void st8(void* p, const float (&r)[8]) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f16x2 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "r"(f_to_f16x2(r[0], r[1])), "r"(f_to_f16x2(r[2], r[3])), "r"(f_to_f16x2(r[4], r[5])),
+                    "r"(f_to_f16x2(r[6], r[7])) : "memory");
+  }
+  static __device__ __forceinline__ float ld1(const void*) { __trap(); return 0.f; }
+  static __device__ __forceinline__ void st1(void*, float) { __trap(); }
+  static __device__ __forceinline__ float round_trip(float v) { return __half2float(__float2half_rn(v)); }
+};
+
+// vector access of V = 4 or 8 elements
+template <typename T, int V> __device__ __forceinline__ void ldv(const void* p, float (&r)[V]) {
+  static_assert(V == 4 || V == 8, "vector width");
+  if constexpr (V == 4) Elem<T>::ld4(p, r); else Elem<T>::ld8(p, r);
+}
+template <typename T, int V> __device__ __forceinline__ void stv(void* p, const float (&r)[V]) {
+  if constexpr (V == 4) Elem<T>::st4(p, r); else Elem<T>::st8(p, r);
+}
+// required alignment, in bytes, of a V-element vector of T (element-wise types: just the element)
+template <typename T, int V> constexpr int vec_align() {
+  return (Elem<T>::QUAD_ALIGN > Elem<T>::SIZE) ? Elem<T>::SIZE * V : Elem<T>::SIZE;
+}
 
 // compile-time loop
 template <int N, int I = 0, class F>
@@ -232,7 +384,7 @@ __device__ __forceinline__ float cta_sum(float v, float* smem /* >= THREADS/32 f
 // ------------------------------------------------------------------------------------------
 // The streaming kernel.  Op supplies:
 //   using Types = TypeList<...>;            element type of every list
-//   static constexpr int THREADS, UNROLL, MIN_CTAS;
+//   static constexpr int THREADS, UNROLL, MIN_CTAS, VEC;
 //   static constexpr unsigned STORES;       bit k set: list k is written back
 //   struct State;                           per-thread registers
 //   bool  begin(State&) const;              false: whole kernel is a no-op (noop gating)
@@ -250,6 +402,7 @@ mt_stream_kernel(const TableView tv, const Op op) {
   constexpr int NL = Types::size;
   constexpr int THREADS = Op::THREADS;
   constexpr int U = Op::UNROLL;
+  constexpr int V = Op::VEC;   // elements per vector access: 4 (128-bit fp32) or 8 (256-bit fp32, 128-bit 16-bit types)
   __shared__ float red_smem[THREADS / 32];
 
   typename Op::State st;
@@ -262,7 +415,7 @@ mt_stream_kernel(const TableView tv, const Op op) {
     const TileLoc L = locate_tile(tv, tile);
     op.tile_begin(st, L);
 
-    // base address of this tile in every list + common head peel to reach quad alignment
+    // base address of this tile in every list + common head peel to reach vector alignment
     char* base[NL];
     int head = -1;
     bool vec_ok = true;
@@ -271,22 +424,23 @@ mt_stream_kernel(const TableView tv, const Op op) {
       unsigned long long a = __ldg(tv.ptrs + (size_t)k.value * tv.ntensors + L.tensor);
       a += (unsigned long long)L.off * Elem<T>::SIZE;
       base[k.value] = reinterpret_cast<char*>(a);
-      constexpr int P = Elem<T>::QUAD_ALIGN / Elem<T>::SIZE;  // alignment period in elements
+      constexpr int A = vec_align<T, V>();
+      constexpr int P = A / Elem<T>::SIZE;  // alignment period in elements
       if constexpr (P > 1) {
-        const int mis = (int)(a % Elem<T>::QUAD_ALIGN) / Elem<T>::SIZE;  // elements past a boundary
+        const int mis = (int)(a % A) / Elem<T>::SIZE;  // elements past a boundary
         const int hk = (P - mis) % P;
-        static_assert(P == 4, "all vectorised element types have a 4-element period");
+        static_assert(P == V, "all vectorised element types have a V-element period");
         if (head < 0) head = hk; else vec_ok = vec_ok && (head == hk);
       }
     });
     if (head < 0) head = 0;
     if (!vec_ok || head > L.len) head = L.len;  // phases disagree: whole tile on the scalar path
-    const int nq = (L.len - head) >> 2;
-    const int tail0 = head + (nq << 2);
+    const int nq = (L.len - head) / V;
+    const int tail0 = head + nq * V;
 
-    // ---- vector body: UNROLL quads per thread in flight, all loads issued before any math
+    // ---- vector body: UNROLL vectors per thread in flight, all loads issued before any math
     for (int q0 = 0; q0 < nq; q0 += THREADS * U) {
-      float x[U][NL][4];
+      float x[U][NL][V];
 #pragma unroll
       for (int u = 0; u < U; u++) {
         const int q = q0 + tid + u * THREADS;
@@ -294,10 +448,10 @@ mt_stream_kernel(const TableView tv, const Op op) {
           static_for<NL>([&](auto k) {
             using T = typename Types::template at<k.value>;
             if (lmask & (1u << k.value)) {
-              Elem<T>::ld4(base[k.value] + ((size_t)head + ((size_t)q << 2)) * Elem<T>::SIZE, x[u][k.value]);
+              ldv<T, V>(base[k.value] + ((size_t)head + (size_t)q * V) * Elem<T>::SIZE, x[u][k.value]);
             } else {
 #pragma unroll
-              for (int i = 0; i < 4; i++) x[u][k.value][i] = 0.f;
+              for (int i = 0; i < V; i++) x[u][k.value][i] = 0.f;
             }
           });
         }
@@ -307,7 +461,7 @@ mt_stream_kernel(const TableView tv, const Op op) {
         const int q = q0 + tid + u * THREADS;
         if (q < nq) {
 #pragma unroll
-          for (int i = 0; i < 4; i++) {
+          for (int i = 0; i < V; i++) {
             float e[NL];
 #pragma unroll
             for (int k = 0; k < NL; k++) e[k] = x[u][k][i];
@@ -319,14 +473,14 @@ mt_stream_kernel(const TableView tv, const Op op) {
             using T = typename Types::template at<k.value>;
             if constexpr ((Op::STORES >> k.value) & 1u) {
               if (smask & (1u << k.value))
-                Elem<T>::st4(base[k.value] + ((size_t)head + ((size_t)q << 2)) * Elem<T>::SIZE, x[u][k.value]);
+                stv<T, V>(base[k.value] + ((size_t)head + (size_t)q * V) * Elem<T>::SIZE, x[u][k.value]);
             }
           });
         }
       }
     }
 
-    // ---- scalar head/tail (<= 6 elements when vectorised, the whole tile otherwise)
+    // ---- scalar head/tail (< 2*V elements when vectorised, the whole tile otherwise)
     const int nscalar = head + (L.len - tail0);
     for (int s = tid; s < nscalar; s += THREADS) {
       const int i = (s < head) ? s : (tail0 + (s - head));
@@ -366,6 +520,7 @@ struct OpBase {
   static constexpr int THREADS = 256;
   static constexpr int UNROLL = 4;
   static constexpr int MIN_CTAS = 4;
+  static constexpr int VEC = 4;
   __device__ __forceinline__ unsigned store_mask() const { return 0xffffffffu; }
   template <class S> __device__ __forceinline__ bool begin(S&) const { return true; }
   template <class S> __device__ __forceinline__ void tile_begin(S&, const TileLoc&) const {}

@@ -9,7 +9,26 @@
 #include <cmath>
 #include "mt_dispatch.h"
 
+// Vector width (elements per access) and vectors in flight per thread; swept on B200
+// (profiles/sweep_vec_r01.txt).
+#ifndef B200MT_ADAM_VEC
+#define B200MT_ADAM_VEC 4
+#endif
+#ifndef B200MT_ADAM_UNROLL
+#define B200MT_ADAM_UNROLL 2
+#endif
+#ifndef B200MT_NVLS_VEC
+#define B200MT_NVLS_VEC 8
+#endif
+#ifndef B200MT_NVLS_UNROLL
+#define B200MT_NVLS_UNROLL 2
+#endif
+
 namespace b200mt {
+
+template <typename T> struct is_mc { static constexpr bool value = false; };
+template <> struct is_mc<mc_bf16> { static constexpr bool value = true; };
+template <> struct is_mc<mc_f16> { static constexpr bool value = true; };
 
 // ---- amp_C.multi_tensor_adam ------------------------------------------------------------------
 // lists [g, p, m, v] (+ optional p_copy).  Per-element math follows
@@ -19,9 +38,10 @@ struct AdamOp : OpBase {
   using Types = typename std::conditional<COPY, TypeList<Tg, Tp, Tp, Tp, Tc>, TypeList<Tg, Tp, Tp, Tp>>::type;
   static constexpr int NL = COPY ? 5 : 4;
   static constexpr unsigned STORES = COPY ? 0b11110 : 0b01110;
-  static constexpr int UNROLL = 2;
+  static constexpr int UNROLL = B200MT_ADAM_UNROLL;
+  static constexpr int VEC = B200MT_ADAM_VEC;
   static constexpr int THREADS = 256;
-  static constexpr int MIN_CTAS = 4;
+  static constexpr int MIN_CTAS = (VEC * UNROLL > 8) ? 2 : 4;
   float beta1, beta2, bc1, bc2, eps, lr, decay, grad_scale;
   int mode;
   __device__ __forceinline__ unsigned load_mask() const { return 0b01111; }
@@ -55,9 +75,10 @@ struct DistAdamOp : OpBase {
   using Types = typename std::conditional<COPY, TypeList<float, float, float, Tg, Tg>, TypeList<float, float, float, Tg>>::type;
   static constexpr int NL = COPY ? 5 : 4;
   static constexpr unsigned STORES = COPY ? 0b10111 : 0b00111;
-  static constexpr int UNROLL = 2;
+  static constexpr int UNROLL = is_mc<Tg>::value ? B200MT_NVLS_UNROLL : B200MT_ADAM_UNROLL;
+  static constexpr int VEC = is_mc<Tg>::value ? B200MT_NVLS_VEC : B200MT_ADAM_VEC;
   static constexpr int THREADS = 256;
-  static constexpr int MIN_CTAS = 4;
+  static constexpr int MIN_CTAS = (VEC * UNROLL > 8) ? 2 : 4;
   struct State { float b1, b2, eps, decay, bc1, bc2; };
   const float *pt_beta1, *pt_beta2, *pt_eps, *pt_decay;
   const int* pt_bias_correction;
@@ -96,9 +117,10 @@ struct ContribAdamOp : OpBase {
   using Types = typename std::conditional<COPY, TypeList<Tp, Tp, Tp, Tg, Tg>, TypeList<Tp, Tp, Tp, Tg>>::type;
   static constexpr int NL = COPY ? 5 : 4;
   static constexpr unsigned STORES = COPY ? 0b10111 : 0b00111;
-  static constexpr int UNROLL = 2;
+  static constexpr int UNROLL = B200MT_ADAM_UNROLL;
+  static constexpr int VEC = B200MT_ADAM_VEC;
   static constexpr int THREADS = 256;
-  static constexpr int MIN_CTAS = 4;
+  static constexpr int MIN_CTAS = (VEC * UNROLL > 8) ? 2 : 4;
   float b1, b2, eps, grad_scale, step_size, decay;
   int mode;
   __device__ __forceinline__ unsigned load_mask() const { return 0b01111; }
@@ -197,6 +219,47 @@ extern "C" int b200mt_dist_adam(const b200mt_lists* L, int chunk_size, int32_t* 
     DistAdamOp<Tg, false> op; fill(op);
     return launch_stream(tv, op, stream);
   });
+}
+
+// The sharded step as ONE kernel over NVSwitch multicast memory: list 3 (g) and list 4 (p_copy) are
+// addresses inside multicast objects; the gradient load reduces over all ranks in the switch and the
+// parameter store is replicated to all ranks by the switch.  Same math as b200mt_dist_adam.
+extern "C" int b200mt_dist_adam_nvls(const b200mt_lists* L, int chunk_size, int32_t* noop,
+                                     const float* pt_beta1, const float* pt_beta2,
+                                     const int32_t* pt_bias_correction, const float* pt_eps,
+                                     const float* pt_weight_decay, float lr, float grad_scale, int step,
+                                     int mode, void* stream_) {
+  (void)noop;
+  if (check_common(L, chunk_size)) return 1;
+  B200MT_CHECK(pt_beta1 && pt_beta2 && pt_bias_correction && pt_eps && pt_weight_decay,
+               "per-tensor hyper-parameter array is NULL");
+  B200MT_CHECK(L->depth == 5, "dist_adam_nvls: expected [p32, m32, v32, g_multicast, p_copy_multicast]");
+  B200MT_CHECK(L->dtype[0] == B200MT_F32 && L->dtype[1] == B200MT_F32 && L->dtype[2] == B200MT_F32,
+               "dist_adam_nvls: p, m, v must be fp32");
+  B200MT_CHECK(L->dtype[3] == L->dtype[4] && (L->dtype[3] == B200MT_BF16 || L->dtype[3] == B200MT_F16),
+               "dist_adam_nvls: g and p_copy must both be Half or both BFloat16");
+  for (int t = 0; t < L->ntensors; t++) {
+    B200MT_CHECK(L->numel[t] % B200MT_NVLS_VEC == 0, "dist_adam_nvls: fragment %d has %lld elements; multicast fragments "
+                 "must be multiples of %d elements", t, (long long)L->numel[t], B200MT_NVLS_VEC);
+    for (int d = 0; d < 5; d++) {
+      const int al = (d < 3 ? 4 : 2) * B200MT_NVLS_VEC;
+      B200MT_CHECK(((uintptr_t)L->ptrs[(size_t)d * L->ntensors + t]) % al == 0,
+                   "dist_adam_nvls: list %d fragment %d is not %d-byte aligned", d, t, al);
+    }
+  }
+  CallGuard guard(L->device);
+  if (guard.status) return 1;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  TableView tv;
+  if (acquire_table(L, 5, 5, elementwise_tiling(), stream, &tv)) return 1;
+  auto run = [&](auto op) {
+    op.pt_beta1 = pt_beta1; op.pt_beta2 = pt_beta2; op.pt_eps = pt_eps; op.pt_decay = pt_weight_decay;
+    op.pt_bias_correction = pt_bias_correction; op.lr = lr; op.grad_scale = grad_scale;
+    op.step = step; op.mode = mode;
+    return launch_stream(tv, op, stream);
+  };
+  if (L->dtype[3] == B200MT_BF16) return run(DistAdamOp<mc_bf16, true>());
+  return run(DistAdamOp<mc_f16, true>());
 }
 
 extern "C" int b200mt_contrib_adam(const b200mt_lists* L, int chunk_size, int32_t* noop, float lr,

@@ -3,6 +3,13 @@
 //   b200mt_axpby  <- amp_C.multi_tensor_axpby  (csrc/multi_tensor_axpby_kernel.cu:27-157)
 #include "mt_dispatch.h"
 
+#ifndef B200MT_SCALE_VEC
+#define B200MT_SCALE_VEC 4
+#endif
+#ifndef B200MT_SCALE_UNROLL
+#define B200MT_SCALE_UNROLL 4
+#endif
+
 namespace b200mt {
 
 __device__ __forceinline__ bool nonfinite(float v) {
@@ -15,7 +22,8 @@ template <typename Tin, typename Tout>
 struct ScaleOp : OpBase {
   using Types = TypeList<Tin, Tout>;
   static constexpr unsigned STORES = 0b10;
-  static constexpr int UNROLL = 4;
+  static constexpr int UNROLL = B200MT_SCALE_UNROLL;
+  static constexpr int VEC = B200MT_SCALE_VEC;
   struct State { bool bad = false; };
   float scale;
   int* noop;

@@ -1,0 +1,101 @@
+"""GPU (needs >= 2 devices, NCCL): DistributedFusedAdam with the real kernels, sharded over 2 ranks,
+against the unsharded mixed-precision Adam on the rank-averaged gradient -- the comparison
+tests/L0/run_optimizers/test_dist_adam.py makes (DistributedFusedAdam vs FusedAdam, atol 1e-3)."""
+import os
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank, world, port, K, zero_copy, fused, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    for p in (os.path.join(ROOT, "rocm-apex_b200"), ROOT):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        import amp_C
+        from apex.contrib.optimizers import DistributedFusedAdam
+        shapes = [(1024, 300), (4096,), (5,), (3000, 77), (1,), (65536,)]
+        g0 = torch.Generator().manual_seed(7)
+        init = [torch.randn(s, generator=g0) * 0.1 for s in shapes]
+        params = [torch.nn.Parameter(t.to(dev).bfloat16()) for t in init]
+        opt = DistributedFusedAdam(params, lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=0.01, dwu_num_blocks=K,
+                                   dwu_num_chunks=1, compute_L2_grad_norm=not fused, overlap_reductions=False,
+                                   zero_copy_params=zero_copy, fused_collectives=fused)
+        opt.set_global_scale(8.0)
+        # unsharded check: our own mixed-precision multi_tensor_adam [g, p32, m32, v32, p_copy] on the averaged grads
+        m32 = [t.to(dev).bfloat16().float() for t in init]
+        mm = [torch.zeros_like(t) for t in m32]
+        vv = [torch.zeros_like(t) for t in m32]
+        pc = [torch.zeros_like(t, dtype=torch.bfloat16) for t in m32]
+        flag = torch.zeros(1, dtype=torch.int32, device=dev)
+        for it in range(1, 5):
+            per_rank = []
+            for r in range(world):
+                gr = torch.Generator().manual_seed(100 * it + r)
+                per_rank.append([(torch.randn(s, generator=gr) * 8.0).to(dev).bfloat16() for s in shapes])
+            for p, g in zip(params, per_rank[rank]):
+                p.grad = g.clone()
+            opt.complete_reductions()
+            opt.step()
+            avg = [sum((gs[i].float() / world).bfloat16().float() for gs in per_rank).bfloat16() for i in range(len(shapes))]
+            amp_C.multi_tensor_adam(65536, flag, [[a.float() / 8.0 for a in avg], m32, mm, vv, pc], 1e-2, 0.9, 0.99, 1e-8, it, 1, 1, 0.01)
+            want_norm = torch.sqrt(sum((a.float() ** 2).sum() for a in avg))
+            if not fused:
+                assert abs(opt.L2_grad_norm - float(want_norm)) <= 1e-3 * float(want_norm)
+            for pi, (p, c) in enumerate(zip(params, pc)):
+                # bf16 parameters: bit-exact expected, one bf16 ulp allowed where NCCL's summation order differs
+                a, b = p.detach().float().reshape(-1), c.float().reshape(-1)
+                # fused_collectives: the gradient sum is formed inside the NVSwitch (multimem.ld_reduce) and
+                # comes back rounded to bf16 by the switch, which is not always the round-to-nearest-even of the
+                # fp32 sum this check uses: a gradient may differ by one bf16 ulp (2^-8 relative), and the Adam
+                # update (|u| <~ 3, lr 1e-2) turns that into at most ~lr*3*2^-7 = 2.4e-4 absolute on p
+                atol = 2.5e-4 if fused else 1e-6
+                bad = (a - b).abs() > (8e-3 * b.abs() + atol)
+                if bad.any():
+                    idx = torch.nonzero(bad).reshape(-1)
+                    raise AssertionError("it %d rank %d param %d: %d/%d differ, first idx %d..last %d, got %r want %r" % (
+                        it, rank, pi, int(bad.sum()), a.numel(), int(idx[0]), int(idx[-1]), float(a[idx[0]]), float(b[idx[0]])))
+        # master shards reassemble to the unsharded fp32 masters
+        L = opt._layout
+        full = torch.zeros(L["total"], device=dev)
+        gathered = [torch.zeros_like(opt._fp32_p) for _ in range(world)]
+        dist.all_gather(gathered, opt._fp32_p)
+        for r in range(world):
+            for k in range(K):
+                lo = k * L["chunk"] + r * L["shard"]
+                full[lo:lo + L["shard"]] = gathered[r][k * L["shard"]:(k + 1) * L["shard"]]
+        for off, t in zip(L["offsets"], m32):
+            got = full[off:off + t.numel()].view_as(t)
+            assert torch.allclose(got, t, rtol=1e-5, atol=2.5e-4 if fused else 1e-6)
+        out.put((rank, "ok"))
+    except Exception:
+        import traceback
+        out.put((rank, "FAIL: " + traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("K,zero_copy,fused", [(1, False, False), (4, True, False), (1, False, True), (1, True, True)])
+def test_sharded_adam_matches_unsharded_world2_nccl(K, zero_copy, fused):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29700 + K + (20 if fused else 0) + (40 if zero_copy else 0)
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, K, zero_copy, fused, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in results:
+        assert msg == "ok", "rank %d: %s" % (rank, msg)
