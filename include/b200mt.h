@@ -158,6 +158,16 @@ int b200mt_dist_adam_nvls(const b200mt_lists* lists, int chunk_size, int32_t* no
                           const float* per_tensor_weight_decay, float lr, float grad_scale, int step,
                           int mode, void* stream);
 
+/* ---- b200mt_nvls_reduce_scatter / b200mt_nvls_all_gather -- the two collectives of the sharded step
+ * (torch.distributed.reduce_scatter / all_gather at apex/contrib/optimizers/distributed_fused_adam.py:409,477)
+ * as stand-alone kernels over NVSwitch multicast memory, for callers that want them unfused.
+ * reduce_scatter: lists = [g_mc, out]: out = sum over ranks of g (multimem.ld_reduce, fp32 accumulation);
+ * all_gather:     lists = [in, out_mc]: in is replicated into every rank's buffer (multimem.st).
+ * The *_mc lists hold multicast addresses; dtype Half or BFloat16; fragments are multiples of 8 elements,
+ * 16-byte aligned.  The caller provides the cross-GPU barriers, as for b200mt_dist_adam_nvls. */
+int b200mt_nvls_reduce_scatter(const b200mt_lists* lists, int chunk_size, void* stream);
+int b200mt_nvls_all_gather(const b200mt_lists* lists, int chunk_size, void* stream);
+
 /* ---- fused_adam_cuda.adam_mt / maybe_cast_mt / strided_check_finite
  *      (apex/contrib/csrc/optimizers/fused_adam_cuda_kernel.cu:283-387, :939-960, :785-812)
  * adam_mt lists = [p, m, v, g] or [p, m, v, g, p_copy]; step_size form (eps not rescaled). */

@@ -405,6 +405,15 @@ mt_stream_kernel(const TableView tv, const Op op) {
   constexpr int V = Op::VEC;   // elements per vector access: 4 (128-bit fp32) or 8 (256-bit fp32, 128-bit 16-bit types)
   __shared__ float red_smem[THREADS / 32];
 
+  // Programmatic dependent launch (no-ops unless the launch asked for it): let the next kernel of the
+  // stream become resident as soon as every CTA of this grid has started, and do this CTA's tile lookup
+  // -- which reads only the descriptor table, never data of the previous kernel -- before waiting for
+  // the previous kernel to finish and flush.
+  asm volatile("griddepcontrol.launch_dependents;");
+  TileLoc L0 = {};
+  if ((int)blockIdx.x < tv.ntiles) L0 = locate_tile(tv, blockIdx.x);
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+
   typename Op::State st;
   if (!op.begin(st)) return;
   const unsigned lmask = op.load_mask();
@@ -412,7 +421,7 @@ mt_stream_kernel(const TableView tv, const Op op) {
   const int tid = threadIdx.x;
 
   for (int tile = blockIdx.x; tile < tv.ntiles; tile += gridDim.x) {
-    const TileLoc L = locate_tile(tv, tile);
+    const TileLoc L = (tile == (int)blockIdx.x) ? L0 : locate_tile(tv, tile);
     op.tile_begin(st, L);
 
     // base address of this tile in every list + common head peel to reach vector alignment

@@ -19,6 +19,7 @@ static std::atomic<int64_t> g_launches{0}, g_uploads{0}, g_hits{0};
 static std::recursive_mutex g_mu;
 static int g_tile_elems = 0;  // 0 = not yet initialised
 static int g_grid_cap = 0;    // 0 = one CTA per tile
+static bool g_pdl = false;    // programmatic dependent launch of the streaming kernels
 
 int set_error(const char* fmt, ...) {
   char buf[1024];
@@ -47,6 +48,12 @@ static void init_tuning() {
   g_tile_elems = 4096;  // swept on B200 (profiles/sweep_tiles_r01.txt): one CTA per 4096-element tile is fastest
   if (const char* e = getenv("B200MT_TILE_ELEMS")) { int v = atoi(e); if (v >= 64) g_tile_elems = v; }
   if (const char* e = getenv("B200MT_GRID_CAP")) { int v = atoi(e); if (v > 0) g_grid_cap = v; }
+  if (const char* e = getenv("B200MT_PDL")) g_pdl = atoi(e) != 0;
+}
+
+bool pdl_enabled() {
+  init_tuning();
+  return g_pdl;
 }
 
 Tiling elementwise_tiling() {

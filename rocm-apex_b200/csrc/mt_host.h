@@ -63,11 +63,28 @@ int acquire_table(const b200mt_lists* L, int expect_depth_min, int expect_depth_
 int acquire_scratch(cudaStream_t stream, size_t bytes, void** out);
 
 int grid_for(int ntiles);
+bool pdl_enabled();   // env B200MT_PDL (default on): launch streaming kernels with programmatic stream serialization
 
 template <class Op>
-int launch_stream(const TableView& tv, const Op& op, cudaStream_t stream) {
+int launch_stream(const TableView& tv, const Op& op, cudaStream_t stream, bool allow_pdl = true) {
   if (tv.ntiles <= 0) return 0;
-  mt_stream_kernel<Op><<<grid_for(tv.ntiles), Op::THREADS, 0, stream>>>(tv, op);
+  if (allow_pdl && pdl_enabled()) {
+    // Programmatic dependent launch: this grid may become resident while the previous kernel of the
+    // stream drains its last wave; it touches nothing that kernel produced before griddepcontrol.wait.
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid_for(tv.ntiles));
+    cfg.blockDim = dim3(Op::THREADS);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    B200MT_CUDA(cudaLaunchKernelEx(&cfg, mt_stream_kernel<Op>, tv, op));
+  } else {
+    mt_stream_kernel<Op><<<grid_for(tv.ntiles), Op::THREADS, 0, stream>>>(tv, op);
+  }
   count_launch();
   B200MT_CUDA(cudaGetLastError());
   return 0;

@@ -59,6 +59,54 @@ extern "C" int b200mt_maybe_cast(const b200mt_lists* L, int chunk_size, const in
   });
 }
 
+// Stand-alone collectives over NVSwitch multicast memory, built from the same streaming kernel:
+//   reduce-scatter: lists = [g_mc (multicast address of this rank's shard), out (local)]
+//                   out = sum over ranks of g, reduced inside the switch (multimem.ld_reduce)
+//   all-gather:     lists = [in (local shard), out_mc (multicast address of the shard's slot)]
+//                   one store, replicated into every rank's buffer by the switch (multimem.st)
+// Fragments must be multiples of 8 elements and 16-byte aligned.  dtype: Half or BFloat16.
+template <typename Tin, typename Tout>
+struct McCopyOp : OpBase {
+  using Types = TypeList<Tin, Tout>;
+  static constexpr unsigned STORES = 0b10;
+  static constexpr int UNROLL = 4;
+  static constexpr int VEC = 8;
+  __device__ __forceinline__ unsigned load_mask() const { return 0b01; }
+  __device__ __forceinline__ void elem(State&, float (&x)[2]) const { x[1] = x[0]; }
+};
+
+static int nvls_copy(const b200mt_lists* L, int chunk_size, bool reduce, void* stream_) {
+  if (check_common(L, chunk_size)) return 1;
+  B200MT_CHECK(L->depth == 2, "expected two lists");
+  B200MT_CHECK(L->dtype[0] == L->dtype[1] && (L->dtype[0] == B200MT_BF16 || L->dtype[0] == B200MT_F16),
+               "nvls collectives: both lists must be Half or both BFloat16");
+  for (int t = 0; t < L->ntensors; t++) {
+    B200MT_CHECK(L->numel[t] % 8 == 0, "nvls collectives: fragment %d is not a multiple of 8 elements", t);
+    for (int d = 0; d < 2; d++)
+      B200MT_CHECK(((uintptr_t)L->ptrs[(size_t)d * L->ntensors + t]) % 16 == 0,
+                   "nvls collectives: list %d fragment %d is not 16-byte aligned", d, t);
+  }
+  CallGuard guard(L->device);
+  if (guard.status) return 1;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  TableView tv;
+  if (acquire_table(L, 2, 2, elementwise_tiling(), stream, &tv)) return 1;
+  const bool bf = L->dtype[0] == B200MT_BF16;
+  if (reduce) {
+    if (bf) return launch_stream(tv, McCopyOp<mc_bf16, __nv_bfloat16>(), stream);
+    return launch_stream(tv, McCopyOp<mc_f16, __half>(), stream);
+  }
+  if (bf) return launch_stream(tv, McCopyOp<__nv_bfloat16, mc_bf16>(), stream);
+  return launch_stream(tv, McCopyOp<__half, mc_f16>(), stream);
+}
+
+extern "C" int b200mt_nvls_reduce_scatter(const b200mt_lists* L, int chunk_size, void* stream) {
+  return nvls_copy(L, chunk_size, true, stream);
+}
+extern "C" int b200mt_nvls_all_gather(const b200mt_lists* L, int chunk_size, void* stream) {
+  return nvls_copy(L, chunk_size, false, stream);
+}
+
 extern "C" int b200mt_strided_check_finite(int32_t* noop, const void* p, int dtype, int64_t numel,
                                            int stride, int clear_overflow_first, int device,
                                            void* stream_) {

@@ -134,7 +134,8 @@ extern "C" int b200mt_l2norm_flat_noalloc(const void* x, int dtype, int64_t nume
   int rc = dispatch_f32_f16_bf16(dtype, "b200mt_l2norm_flat_noalloc", [&](auto t) {
     FlatL2NormOp<typename decltype(t)::type> op;
     op.partials = ns.partials;
-    return launch_stream(tv, op, stream);
+    // no programmatic early start: the descriptor table itself was written by the kernel just before
+    return launch_stream(tv, op, stream, false);
   });
   if (rc) return 1;
   return launch_norm_cleanup(tv, ns, 1, noop, 0, ret, nullptr, nullptr, nullptr, stream);
