@@ -95,7 +95,9 @@ def run_sharded(args):
     dist.init_process_group("nccl", device_id=dev)
     model_name = os.environ.get("B200MT_SHARDED_MODEL", "llama3_8b")
     K = int(os.environ.get("B200MT_SHARDED_CHUNKS", "8"))
-    fused = os.environ.get("B200MT_SHARDED_FUSED", "0") == "1"   # one multimem kernel instead of RS -> Adam -> AG
+    # default: the whole step as one multimem kernel (DistributedFusedAdam(fused_collectives=True));
+    # B200MT_SHARDED_FUSED=0 times the NCCL pipeline RS -> Adam -> AG instead (profiles/sharded_bench_r01.jsonl has both)
+    fused = os.environ.get("B200MT_SHARDED_FUSED", "1") == "1"
     if fused:
         K = 1
     shapes = param_shapes.MODELS[model_name]()

@@ -91,6 +91,13 @@ def _load():
 
 lib, EXPORTS = _load()
 
+try:   # optional native list walker (build_packer.py); the Python walker below is its exact equivalent
+    from _b200mt_pack import pack_lists as _fast_pack
+except ImportError:
+    _fast_pack = None
+if os.environ.get("B200MT_PY_PACK"):
+    _fast_pack = None
+
 
 def check(rc):
     """Turn a non-zero C return code into the RuntimeError the reference's TORCH_CHECK would raise."""
@@ -147,6 +154,22 @@ def pack(tensor_lists, depth=None):
     ntensors = len(first)
     if ntensors <= 0:
         raise RuntimeError("tensor_lists[0].size() is not > 0")
+    if _fast_pack is not None:
+        # native walk of the lists (csrc/packer.cpp): same checks, same messages, ~50x less host time
+        ptrs = np.empty(nlists * ntensors, dtype=np.uint64)
+        numel = np.empty(ntensors, dtype=np.int64)
+        r = _fast_pack(tensor_lists, ptrs.ctypes.data, numel.ctypes.data, nlists * ntensors)
+        if r is not None:
+            _, _, codes, dev_index = r
+            p = Packed()
+            p.ptrs, p.numel, p.ntensors, p.depth, p.device = ptrs, numel, ntensors, nlists, dev_index
+            s = Lists()
+            s.ptrs, s.numel, s.ntensors, s.depth, s.device = ptrs.ctypes.data, numel.ctypes.data, ntensors, nlists, dev_index
+            for d, c in enumerate(codes):
+                s.dtype[d] = c
+            p.struct = s
+            return p
+        # r is None: some entry is not a torch tensor (e.g. a RawBuffer) -> generic path below
     ref_device = first[0].device
     if ref_device.type != "cuda":
         raise RuntimeError("expected input to be on cuda")

@@ -8,10 +8,14 @@
 namespace b200mt {
 
 // Pass 1: per-tile sum of squares in fp32 (csrc/multi_tensor_l2norm_kernel.cu:71-75).
+#ifndef B200MT_NORM16_VEC
+#define B200MT_NORM16_VEC 8   // 16-bit inputs: 8 elements = one 128-bit load per access
+#endif
 template <typename Tx>
 struct L2NormOp : OpBase {
   using Types = TypeList<Tx>;
   static constexpr unsigned STORES = 0;
+  static constexpr int VEC = (Elem<Tx>::SIZE == 2) ? B200MT_NORM16_VEC : 4;
   static constexpr int UNROLL = 4;
   static constexpr int THREADS = 256;
   struct State { float acc = 0.f; };
@@ -66,7 +70,8 @@ extern "C" int b200mt_l2norm(const b200mt_lists* L, int chunk_size, int32_t* noo
   if (guard.status) return 1;
   cudaStream_t stream = (cudaStream_t)stream_;
   TableView tv;
-  if (acquire_table(L, 1, 1, chunked_tiling(chunk_size), stream, &tv)) return 1;
+  const int tile_scale = (L->dtype[0] == B200MT_F16 || L->dtype[0] == B200MT_BF16) ? 2 : 1;
+  if (acquire_table(L, 1, 1, chunked_tiling(chunk_size, tile_scale), stream, &tv)) return 1;
   void* raw;
   if (acquire_scratch(stream, norm_scratch_bytes(1, tv.ntiles, tv.ntensors), &raw)) return 1;
   NormScratch ns = carve_norm_scratch(raw, 1, tv.ntiles, tv.ntensors);

@@ -12,6 +12,15 @@
 #include "mt_dispatch.h"
 #include "mt_norm.cuh"
 
+// stage 1: 8 elements per access x 1 in flight beats 4 x 2 by 7 % on the mixed-precision lists and
+// 2 % on fp32 (profiles/sweep_variants_r01.txt)
+#ifndef B200MT_LAMB_VEC
+#define B200MT_LAMB_VEC 8
+#endif
+#ifndef B200MT_LAMB_UNROLL
+#define B200MT_LAMB_UNROLL 1
+#endif
+
 namespace b200mt {
 
 // ---- stage 1 (fused with both norm partials) ----------------------------------------------------
@@ -22,9 +31,10 @@ struct LambStage1Op : OpBase {
   using Types = typename std::conditional<DEPTH == 5, TypeList<Tg, Tp, Tp, Tp, Tg>, TypeList<Tg, Tp, Tp, Tp>>::type;
   static constexpr int NL = DEPTH;
   static constexpr unsigned STORES = 0b01101;  // g <- update, m, v
-  static constexpr int UNROLL = 2;
+  static constexpr int UNROLL = B200MT_LAMB_UNROLL;
+  static constexpr int VEC = B200MT_LAMB_VEC;
   static constexpr int THREADS = 256;
-  static constexpr int MIN_CTAS = 4;
+  static constexpr int MIN_CTAS = (VEC * UNROLL > 8) ? 2 : 4;
   struct State { float clip, inv_scale, bc1, bc2, acc_p, acc_u; };
   float beta1, beta2, beta3, eps, decay;
   float bc1_host, bc2_host, max_norm_host;

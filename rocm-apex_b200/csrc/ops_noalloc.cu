@@ -14,9 +14,9 @@
 //  * the array is B200MT_NOALLOC_SCRATCH_BYTES (about 257 KiB) of device memory on EVERY GPU that
 //    loads this library, from load until the process exits, whether or not this function is called;
 //  * inputs needing more than B200MT_NOALLOC_MAX_TILES (65536) scheduling tiles are refused with an
-//    error -- with the default tile of 4096 elements and chunk_size >= 4096 that is 268,435,456
-//    elements; tiny chunk sizes lower it (one tile per chunk at least), a larger B200MT_TILE_ELEMS
-//    raises it;
+//    error -- with the default norm tile of 16384 elements and chunk_size >= 16384 that is
+//    1,073,741,824 elements; small chunk sizes lower it (one tile per chunk at least), and so does a
+//    smaller B200MT_NORM_TILE_ELEMS;
 //  * all calls on a device share the array and it keeps whatever the previous call left in it.  The
 //    function re-initialises the few words that must start at zero itself, at the head of its own
 //    work on the stream, so back-to-back calls on one stream are fine; two calls whose GPU work can
