@@ -11,7 +11,9 @@ template <typename Tin, typename Tout>
 struct MaybeCastOp : OpBase {
   using Types = TypeList<Tin, Tout>;
   static constexpr unsigned STORES = 0b10;
-  static constexpr int UNROLL = 4;
+  static constexpr bool ANY16 = Elem<Tin>::SIZE == 2 || Elem<Tout>::SIZE == 2;   // as for ScaleOp
+  static constexpr int UNROLL = ANY16 ? 2 : 4;
+  static constexpr int VEC = ANY16 ? 8 : 4;
   const int* flag;
   __device__ __forceinline__ bool begin(State&) const {
     return !(flag && *reinterpret_cast<const volatile int*>(flag) != 0);

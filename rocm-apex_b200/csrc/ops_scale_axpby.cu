@@ -24,8 +24,11 @@ template <typename Tin, typename Tout>
 struct ScaleOp : OpBase {
   using Types = TypeList<Tin, Tout>;
   static constexpr unsigned STORES = 0b10;
-  static constexpr int UNROLL = B200MT_SCALE_UNROLL;
-  static constexpr int VEC = B200MT_SCALE_VEC;
+  // a 16-bit list wants 8 elements (one 128-bit access) per vector; fp32-only lists are as fast or
+  // faster (small tensor lists) with 4 x 4
+  static constexpr bool ANY16 = Elem<Tin>::SIZE == 2 || Elem<Tout>::SIZE == 2;
+  static constexpr int UNROLL = ANY16 ? B200MT_SCALE_UNROLL : 4;
+  static constexpr int VEC = ANY16 ? B200MT_SCALE_VEC : 4;
   struct State { bool bad = false; };
   float scale;
   int* noop;
