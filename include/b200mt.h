@@ -131,6 +131,20 @@ int b200mt_lamb_stage2(const b200mt_lists* lists, int chunk_size, int32_t* noop,
                        const float* per_tensor_param_norm, const float* per_tensor_update_norm,
                        float lr, float weight_decay, int use_nvlamb, void* stream);
 
+/* ---- amp_C.multi_tensor_adagrad  (csrc/multi_tensor_adagrad.cu:85-100)
+ * lists = [g, p, h], one dtype.  mode 0: L2 (decay folded into g), 1: decoupled decay. */
+int b200mt_adagrad(const b200mt_lists* lists, int chunk_size, int32_t* noop, float lr, float eps, int mode,
+                   float weight_decay, void* stream);
+
+/* ---- amp_C.multi_tensor_novograd  (csrc/multi_tensor_novograd.cu:120-188)
+ * lists = [g, p, m], one dtype.  grad_norms: device float[ntensors], updated in place first
+ * (multi_tensor_norm_out_cuda, csrc/multi_tensor_l2norm_kernel.cu:371-456): norm_type 2 -> L2 blend
+ * sqrt(beta2*gn^2 + (1-beta2)*|g|^2), norm_type 0 -> L-inf blend beta2*gn + (1-beta2)*max|g|; then the update.
+ * The norm pass raises *noop on a non-finite chunk. */
+int b200mt_novograd(const b200mt_lists* lists, int chunk_size, int32_t* noop, float* grad_norms, float lr,
+                    float beta1, float beta2, float eps, int step, int bias_correction, float weight_decay,
+                    int grad_averaging, int moment_mode, int norm_type, void* stream);
+
 /* ---- distributed_adam_cuda.multi_tensor_fused_adam
  *      (apex/contrib/csrc/optimizers/multi_tensor_distopt_adam_kernel.cu:169-228)
  * lists = [p32, m32, v32, g] or [p32, m32, v32, g, p_copy(g's dtype)].  Per-tensor device arrays

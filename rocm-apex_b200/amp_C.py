@@ -147,9 +147,21 @@ def multi_tensor_lamb_stage2_cuda(chunk_size, noop_flag, tensor_lists, per_tenso
                                       _mt.stream_ptr(L.device)))
 
 
-def multi_tensor_adagrad(*args, **kwargs):
-    raise NotImplementedError("multi_tensor_adagrad is outside the fused Adam/LAMB/SGD hot path (SURVEY.md 8f-3)")
+def multi_tensor_adagrad(chunk_size, noop_flag, tensor_lists, lr, epsilon, mode, weight_decay):
+    """[g, p, h] Adagrad, mode 0 L2 / 1 decoupled decay (csrc/multi_tensor_adagrad.cu:85-100)."""
+    L = _mt.pack(tensor_lists, 3)
+    _mt.check(_lib.b200mt_adagrad(L.ref(), int(chunk_size), _mt.noop_ptr(noop_flag), float(lr), float(epsilon),
+                                  int(mode), float(weight_decay), _mt.stream_ptr(L.device)))
 
 
-def multi_tensor_novograd(*args, **kwargs):
-    raise NotImplementedError("multi_tensor_novograd is outside the fused Adam/LAMB/SGD hot path (SURVEY.md 8f-3)")
+def multi_tensor_novograd(chunk_size, noop_flag, tensor_lists, grad_norms, lr, beta1, beta2, epsilon, step,
+                          bias_correction, weight_decay, grad_averaging, moment_mode, norm_type):
+    """[g, p, m] NovoGrad; grad_norms (fp32[T], device) is blended with this step's per-tensor gradient
+    norm in place, then used as the second moment (csrc/multi_tensor_novograd.cu:120-188)."""
+    L = _mt.pack(tensor_lists, 3)
+    if grad_norms.numel() != L.ntensors:
+        raise RuntimeError("grad_norms must hold one value per tensor")
+    _mt.check(_lib.b200mt_novograd(L.ref(), int(chunk_size), _mt.noop_ptr(noop_flag, L.device),
+                                   _mt.dev_ptr(grad_norms, torch.float32, "grad_norms"), float(lr), float(beta1),
+                                   float(beta2), float(epsilon), int(step), int(bias_correction), float(weight_decay),
+                                   int(grad_averaging), int(moment_mode), int(norm_type), _mt.stream_ptr(L.device)))

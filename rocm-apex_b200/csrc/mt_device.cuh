@@ -381,6 +381,26 @@ __device__ __forceinline__ float cta_sum(float v, float* smem /* >= THREADS/32 f
   return r;
 }
 
+// Same shape, max instead of sum (values must be >= 0: the L-infinity norm).  fmaxf drops NaN, as the
+// reference's MaxNormFunctor does (csrc/multi_tensor_l2norm_kernel.cu:132-155).
+template <int THREADS>
+__device__ __forceinline__ float cta_max(float v, float* smem) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int NW = THREADS / 32;
+  __syncthreads();
+  if (lane == 0) smem[warp] = v;
+  __syncthreads();
+  float r = 0.f;
+  if (warp == 0) {
+    r = (lane < NW) ? smem[lane] : 0.f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) r = fmaxf(r, __shfl_xor_sync(0xffffffffu, r, o));
+  }
+  return r;
+}
+
 // ------------------------------------------------------------------------------------------
 // The streaming kernel.  Op supplies:
 //   using Types = TypeList<...>;            element type of every list

@@ -50,6 +50,12 @@ struct CleanupArgs {
   int gated;                 // 1: skip all output when *noop != 0 on entry (the _mp variants)
   float* ret[2];             // per set: global norm out (float[1]) or NULL
   float* ret_per_tensor[2];  // per set: per-tensor norm out (float[ntensors]) or NULL
+  // NovoGrad's norm_out (csrc/multi_tensor_l2norm_kernel.cu:274-297,371-456): partials are per-tile max|x|
+  // (max_mode) or sums of squares, and the per-tensor result is blended into ret_per_tensor in place:
+  //   L2:   out = sqrt(alpha*out^2 + beta*sum x^2)      L-inf: out = alpha*out + beta*max|x|
+  int max_mode;
+  int blend;
+  float alpha, beta;
 };
 
 static __global__ void __launch_bounds__(kCleanupThreads) norm_cleanup_kernel(const CleanupArgs a) {
@@ -71,14 +77,23 @@ static __global__ void __launch_bounds__(kCleanupThreads) norm_cleanup_kernel(co
           float cs = 0.f;
           const int j0 = c * a.ppc;
           const int j1 = min(j0 + a.ppc, nt);
-          for (int j = j0; j < j1; j++) cs += p[j];
+          if (a.max_mode) {
+            for (int j = j0; j < j1; j++) cs = fmaxf(cs, p[j]);
+            acc = fmaxf(acc, cs);
+          } else {
+            for (int j = j0; j < j1; j++) cs += p[j];
+            acc += cs;
+          }
           bad = bad || !isfinite(cs);
-          acc += cs;
         }
-        const float total = cta_sum<kCleanupThreads>(acc, red);
+        const float total = a.max_mode ? cta_max<kCleanupThreads>(acc, red) : cta_sum<kCleanupThreads>(acc, red);
         if (tid == 0) {
           a.totals[(size_t)set * a.ntensors + t] = total;
-          if (a.ret_per_tensor[set]) a.ret_per_tensor[set][t] = sqrtf(total);
+          if (float* out = a.ret_per_tensor[set]) {
+            if (!a.blend) out[t] = sqrtf(total);
+            else if (a.max_mode) out[t] = a.alpha * out[t] + a.beta * total;
+            else out[t] = sqrtf(a.alpha * out[t] * out[t] + a.beta * total);
+          }
         }
       }
     }
@@ -111,8 +126,10 @@ static __global__ void __launch_bounds__(kCleanupThreads) norm_cleanup_kernel(co
 
 inline int launch_norm_cleanup(const TableView& tv, const NormScratch& s, int nsets, int* noop,
                                int gated, float* ret0, float* per0, float* ret1, float* per1,
-                               cudaStream_t stream) {
+                               cudaStream_t stream, int max_mode = 0, int blend = 0, float alpha = 0.f,
+                               float beta = 0.f) {
   CleanupArgs a;
+  a.max_mode = max_mode; a.blend = blend; a.alpha = alpha; a.beta = beta;
   a.tile_prefix = tv.tile_prefix;
   a.ntensors = tv.ntensors; a.ntiles = tv.ntiles; a.ppc = tv.ppc; a.nsets = nsets;
   a.partials = s.partials; a.totals = s.totals; a.counters = s.counters;
