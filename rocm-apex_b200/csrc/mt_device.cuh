@@ -256,6 +256,48 @@ template <> struct Elem<double> {
   static __device__ __forceinline__ float round_trip(float v) { return v; }
 };
 
+// e5m2 bytes (B200MT_U8 lists of maybe_cast / strided_check_finite): the upper byte of an fp16.
+// Packing follows the reference exactly (apex/contrib/csrc/optimizers/fused_adam_cuda_kernel.cu:395-463):
+// add 1/8 of the value's power of two (round half up in magnitude), round to fp16, keep the high byte.
+struct e5m2 {};
+
+__device__ __forceinline__ float e5m2_to_f(unsigned byte) {
+  return __half2float(__ushort_as_half((unsigned short)(byte << 8)));
+}
+__device__ __forceinline__ unsigned f_to_e5m2(float v) {
+  const float pow2 = __uint_as_float(__float_as_uint(v) & 0xFF800000u);
+  return (unsigned)(__half_as_ushort(__float2half_rn(v + pow2 / 8.0f)) >> 8);
+}
+
+template <> struct Elem<e5m2> {
+  static constexpr int SIZE = 1, QUAD_ALIGN = 4;
+  static __device__ __forceinline__ void ld4(const void* p, float (&r)[4]) {
+    const unsigned v = *reinterpret_cast<const unsigned*>(p);
+#pragma unroll
+    for (int i = 0; i < 4; i++) r[i] = e5m2_to_f((v >> (8 * i)) & 0xffu);
+  }
+  static __device__ __forceinline__ void st4(void* p, const float (&r)[4]) {
+    unsigned v = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) v |= f_to_e5m2(r[i]) << (8 * i);
+    *reinterpret_cast<unsigned*>(p) = v;
+  }
+  static __device__ __forceinline__ void ld8(const void* p, float (&r)[8]) {
+    const uint2 v = ld_u2(reinterpret_cast<const uint2*>(p));
+#pragma unroll
+    for (int i = 0; i < 4; i++) { r[i] = e5m2_to_f((v.x >> (8 * i)) & 0xffu); r[4 + i] = e5m2_to_f((v.y >> (8 * i)) & 0xffu); }
+  }
+  static __device__ __forceinline__ void st8(void* p, const float (&r)[8]) {
+    uint2 v = make_uint2(0u, 0u);
+#pragma unroll
+    for (int i = 0; i < 4; i++) { v.x |= f_to_e5m2(r[i]) << (8 * i); v.y |= f_to_e5m2(r[4 + i]) << (8 * i); }
+    st_u2(reinterpret_cast<uint2*>(p), v);
+  }
+  static __device__ __forceinline__ float ld1(const void* p) { return e5m2_to_f(*reinterpret_cast<const unsigned char*>(p)); }
+  static __device__ __forceinline__ void st1(void* p, float v) { *reinterpret_cast<unsigned char*>(p) = (unsigned char)f_to_e5m2(v); }
+  static __device__ __forceinline__ float round_trip(float v) { return e5m2_to_f(f_to_e5m2(v)); }
+};
+
 // Multicast (NVLS) views of 16-bit lists, for the fused compute+collective kernels.  The pointer is
 // an address inside a CUDA multicast object bound to the same symmetric buffer on every GPU of the
 // NVSwitch domain:

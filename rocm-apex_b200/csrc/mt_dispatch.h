@@ -24,6 +24,13 @@ int dispatch_f64_f32_f16_bf16(int dtype, const char* name, F&& f) {
   return dispatch_f32_f16_bf16(dtype, name, f);
 }
 
+// float / half / bfloat16 / byte, the byte being an e5m2 value (DISPATCH_FLOAT_HALF_AND_BYTE, csrc/type_shim.h:63)
+template <class F>
+int dispatch_f32_f16_bf16_u8(int dtype, const char* name, F&& f) {
+  if (dtype == B200MT_U8) return f(Tag<e5m2>{});
+  return dispatch_f32_f16_bf16(dtype, name, f);
+}
+
 template <class F>
 int dispatch_f32_f16(int dtype, const char* name, F&& f) {
   switch (dtype) {

@@ -52,8 +52,9 @@ extern "C" int b200mt_maybe_cast(const b200mt_lists* L, int chunk_size, const in
   cudaStream_t stream = (cudaStream_t)stream_;
   TableView tv;
   if (acquire_table(L, 2, 2, elementwise_tiling(), stream, &tv)) return 1;
-  return dispatch_f32_f16_bf16(L->dtype[0], "maybe_cast_cuda_mt_kernel", [&](auto ti) {
-    return dispatch_f32_f16_bf16(L->dtype[1], "maybe_cast_cuda_mt_kernel", [&](auto to) {
+  // the reference dispatches float / half / byte (e5m2) on both sides (DISPATCH_FLOAT_HALF_AND_BYTE); bf16 is extra
+  return dispatch_f32_f16_bf16_u8(L->dtype[0], "maybe_cast_cuda_mt_kernel", [&](auto ti) {
+    return dispatch_f32_f16_bf16_u8(L->dtype[1], "maybe_cast_cuda_mt_kernel", [&](auto to) {
       MaybeCastOp<typename decltype(ti)::type, typename decltype(to)::type> op;
       op.flag = overflow_flag;
       return launch_stream(tv, op, stream);
@@ -123,7 +124,7 @@ extern "C" int b200mt_strided_check_finite(int32_t* noop, const void* p, int dty
   long long blocks = clear_overflow_first ? 1 : (niter + threads - 1) / threads;
   if (blocks < 1) blocks = 1;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  return dispatch_f32_f16_bf16(dtype, "check_finite_cuda_kernel", [&](auto t) {
+  return dispatch_f32_f16_bf16_u8(dtype, "check_finite_cuda_kernel", [&](auto t) {
     using T = typename decltype(t)::type;
     strided_check_finite_kernel<T><<<(int)blocks, threads, 0, stream>>>(noop, (const T*)p, numel, stride,
                                                                      clear_overflow_first);

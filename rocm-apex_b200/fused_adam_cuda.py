@@ -44,7 +44,29 @@ def _unsupported(name):
     return f
 
 
-adam = _unsupported("adam")
+def adam(p, p_copy, m, v, g, lr, beta1, beta2, eps, grad_scale, step, mode, bias_correction, decay):
+    """Flat-tensor form of adam_mt (fused_adam_cuda.cpp:27-38, fused_adam_cuda_kernel.cu:202-281): p_copy may be an
+    empty tensor when no low-precision copy is wanted."""
+    n = p.numel()
+    for name, t in (("m", m), ("v", v), ("g", g)):
+        if t.numel() != n:
+            raise RuntimeError("number of elements in %s and p tensors should be equal" % name)
+    if p_copy.numel() not in (0, n):
+        raise RuntimeError("number of elements in p_copy and p tensors should be equal, or p_copy should be empty")
+    lists = [[p], [m], [v], [g]] + ([[p_copy]] if p_copy.numel() else [])
+    dummy = torch.zeros(1, dtype=torch.int32, device=p.device)
+    adam_mt(2048 * 32, dummy, lists, lr, beta1, beta2, eps, grad_scale, step, mode, bias_correction, decay)
+
+
+def maybe_cast(overflow_flag, p_in, p_out):
+    """Flat-tensor form of maybe_cast_mt (fused_adam_cuda.cpp:68-75)."""
+    if p_out.numel() != p_in.numel():
+        raise RuntimeError("number of elements in p_in and p_out should be equal")
+    maybe_cast_mt(2048 * 32, overflow_flag, [[p_in], [p_out]])
+
+
+# reversible_adam / maybe_adam_undo stay out: besides being section 8f-4 material, the reference's undo kernel only
+# reverts every fourth element (`int j = j_start + i*ILP` inside the ILP loop, fused_adam_cuda_kernel.cu:687-690),
+# so there is no well-defined behaviour to be identical to.
 reversible_adam = _unsupported("reversible_adam")
 maybe_adam_undo = _unsupported("maybe_adam_undo")
-maybe_cast = _unsupported("maybe_cast")

@@ -152,3 +152,38 @@ def test_fused_novograd_vs_plain_pytorch():
             p -= lr * ((m[i] / bc1) / (v[i] / bc2 + eps) + wd * p)
         assert max(float((r.float() - t.detach()).abs().max()) for r, t in zip(ref_p, tst_p)) <= 1e-5
     assert opt.param_groups[0]["exp_avg_sq"][1].numel() == 3 and opt.param_groups[0]["exp_avg_sq"][0].numel() == 0
+
+
+def test_e5m2_pack_unpack_matches_reference():
+    """maybe_cast_mt between float/half and e5m2 bytes (fused_adam_cuda_kernel.cu:395-463), bit-exact."""
+    import fused_adam_cuda as ours
+    refm = load_ref("fused_adam_cuda_ref")
+    if refm is None:
+        pytest.skip("oracle/_ref/fused_adam_cuda_ref.so not built")
+    g = torch.Generator(device="cuda").manual_seed(60)
+    sizes = [1, 7, 555, 65537, 33333]
+    for src_dt in (torch.float32, torch.float16):
+        src = [(torch.randn(n, generator=g, device="cuda") * 10.0 ** torch.randint(-3, 4, (1,), device="cuda").float()).to(src_dt) for n in sizes]
+        src[2][5] = 0.0
+        src[3][100] = 70000.0 if src_dt == torch.float32 else 60000.0     # beyond / near the fp16 range
+        packed = [torch.zeros(n, dtype=torch.uint8, device="cuda") for n in sizes]
+        rpacked = [torch.zeros_like(t) for t in packed]
+        ours.maybe_cast_mt(CHUNK, flag_tensor(0), [src, packed])
+        refm.maybe_cast_mt(CHUNK, flag_tensor(0), [src, rpacked])
+        for a, b in zip(packed, rpacked):
+            assert torch.equal(a, b)
+        for out_dt in (torch.float32, torch.float16):
+            un = [torch.zeros(n, dtype=out_dt, device="cuda") for n in sizes]
+            run = [torch.zeros_like(t) for t in un]
+            ours.maybe_cast_mt(CHUNK, flag_tensor(0), [packed, un])
+            refm.maybe_cast_mt(CHUNK, flag_tensor(0), [rpacked, run])
+            for a, b in zip(un, run):
+                assert torch.equal(a.isnan(), b.isnan()) and torch.equal(a.nan_to_num(), b.nan_to_num())
+    # byte tensors through the strided finite check: 0x7c = +inf in e5m2
+    y = torch.full((10000,), 0x3c, dtype=torch.uint8, device="cuda")
+    y[4096] = 0x7c
+    for stride, expect in ((64, 1), (4097, 0)):
+        f, rf = flag_tensor(0), flag_tensor(0)
+        ours.strided_check_finite(f, y, stride, 1)
+        refm.strided_check_finite(rf, y, stride, 1)
+        assert int(f) == int(rf) == expect
