@@ -156,6 +156,28 @@ int b200mt_dist_adam(const b200mt_lists* lists, int chunk_size, int32_t* noop,
                      const float* per_tensor_weight_decay, float lr, float grad_scale, int step,
                      int mode, void* stream);
 
+/* ---- distributed_lamb_cuda.multi_tensor_lamb_compute_update_term / multi_tensor_lamb_update_weights
+ *      (apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb.cpp:3-36, ..._lamb_kernel.cu:108-506)
+ * The sharded LAMB step of DistributedFusedLAMB.  Per-fragment hyper-parameters are device arrays; step,
+ * global_scale, global_grad_norm and lr are device scalars; both kernels return at once when *noop == 1.
+ * stage1 lists = [g, p, m, v, u]: u <- Adam-style update of g/combined_scale (clip folded into combined_scale),
+ *   m, v updated.  Extension: when update_sumsq != NULL it receives, per fragment, the sum of squares of u
+ *   (raw, so that it can be all-reduced over ranks before the square root); pass NULL for reference behaviour.
+ * stage2 lists = [u, p, p_copy]: p -= ratio*u with ratio = lr*param_norm[t]/update_norm[update_norm_offset[t]]
+ *   when use_nvlamb or decay[t] != 0, else lr; p_copy = (its dtype, Half / BFloat16 / e5m2 byte / Float) p. */
+int b200mt_dist_lamb_stage1(const b200mt_lists* lists, int chunk_size, int32_t* noop,
+                            const float* per_tensor_beta1, const float* per_tensor_beta2,
+                            const float* per_tensor_beta3, const int32_t* per_tensor_bias_correction,
+                            const int32_t* step, const float* per_tensor_eps, int mode,
+                            const float* per_tensor_decay, const float* global_scale,
+                            const float* global_grad_norm, float max_grad_norm, float* update_sumsq,
+                            void* stream);
+int b200mt_dist_lamb_stage2(const b200mt_lists* lists, int chunk_size, int32_t* noop,
+                            const float* per_tensor_param_norm, const float* per_tensor_update_norm,
+                            const int64_t* update_norm_offset, const float* lr,
+                            const float* per_tensor_decay, const float* global_grad_norm, int use_nvlamb,
+                            void* stream);
+
 /* ---- b200mt_dist_adam_nvls -- the sharded step of DistributedFusedAdam as ONE kernel (extension; it
  * replaces the reference's three-step sequence reduce_scatter -> multi_tensor_fused_adam -> all_gather,
  * apex/contrib/optimizers/distributed_fused_adam.py:409,443-467,477).

@@ -77,6 +77,8 @@ def _load():
         "b200mt_adagrad": (c_int, [LP, c_int, vp, c_float, c_float, c_int, c_float, vp]),
         "b200mt_novograd": (c_int, [LP, c_int, vp, vp, c_float, c_float, c_float, c_float, c_int, c_int, c_float, c_int,
                                     c_int, c_int, vp]),
+        "b200mt_dist_lamb_stage1": (c_int, [LP, c_int, vp, vp, vp, vp, vp, vp, vp, c_int, vp, vp, vp, c_float, vp, vp]),
+        "b200mt_dist_lamb_stage2": (c_int, [LP, c_int, vp, vp, vp, vp, vp, vp, vp, c_int, vp]),
         "b200mt_nvls_reduce_scatter": (c_int, [LP, c_int, vp]),
         "b200mt_nvls_all_gather": (c_int, [LP, c_int, vp]),
         "b200mt_contrib_adam": (c_int, [LP, c_int, vp, c_float, c_float, c_float, c_float, c_float, c_int,

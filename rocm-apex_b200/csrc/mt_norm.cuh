@@ -91,6 +91,7 @@ static __global__ void __launch_bounds__(kCleanupThreads) norm_cleanup_kernel(co
           a.totals[(size_t)set * a.ntensors + t] = total;
           if (float* out = a.ret_per_tensor[set]) {
             if (!a.blend) out[t] = sqrtf(total);
+            else if (a.blend == 2) out[t] = total;   // raw sum of squares: the caller all-reduces before the sqrt
             else if (a.max_mode) out[t] = a.alpha * out[t] + a.beta * total;
             else out[t] = sqrtf(a.alpha * out[t] * out[t] + a.beta * total);
           }
