@@ -1,5 +1,8 @@
 W=${W:-2}
-for M in bert_large llama3_8b; do
-MODEL=$M timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $W --master-addr 127.0.0.1 --master-port 29861 tools/bench_dist_lamb.py 2>&1 | grep -E '^\{|Error' >> gpurun_out/dist_lamb_n$W.log
+timeout 600 python -m pytest tests/test_ddp.py -m gpu -q > gpurun_out/pytest_ddp.log 2>&1; echo rc=$? >> gpurun_out/pytest_ddp.log
+grep -E "^E  |passed|failed|Error" gpurun_out/pytest_ddp.log | head -20
+rm -f gpurun_out/ddp_n$W.log
+for M in resnet50 bert_large; do
+MODEL=$M timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $W --master-addr 127.0.0.1 --master-port 29871 tools/bench_ddp.py 2>&1 | grep -E '^\{|Error' >> gpurun_out/ddp_n$W.log
 done
-cat gpurun_out/dist_lamb_n$W.log
+cat gpurun_out/ddp_n$W.log
