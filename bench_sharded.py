@@ -109,11 +109,27 @@ def run_sharded(args):
     params = []
     for s in shapes:
         params.append(torch.nn.Parameter((torch.randn(s, generator=gen, device=dev, dtype=torch.float32) * 0.02).to(torch.bfloat16)))
-    opt = DistributedFusedAdam(params, lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1, dwu_num_blocks=K,
-                               dwu_num_chunks=1, predivide=False, overlap_reductions=False, zero_copy_params=True,
-                               fused_collectives=fused)
-    opt.set_global_scale(float(world))          # gradients are summed by the reduce-scatter; the kernel divides by W
-    flat = opt.attach_flat_grads()
+    def make(fused_flag, chunks):
+        o = DistributedFusedAdam(params, lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1, dwu_num_blocks=chunks,
+                                 dwu_num_chunks=1, predivide=False, overlap_reductions=False, zero_copy_params=True,
+                                 fused_collectives=fused_flag)
+        o.set_global_scale(float(world))        # gradients are summed by the reduce-scatter; the kernel divides by W
+        return o, o.attach_flat_grads()
+
+    try:
+        opt, flat = make(fused, K)
+        ok = torch.ones(1, device=dev)
+    except Exception as e:                      # no multicast-capable symmetric memory on this box
+        if not fused:
+            raise
+        sys.stderr.write("bench_sharded: fused multimem path unavailable (%r); timing the NCCL pipeline\n" % (e,))
+        ok = torch.zeros(1, device=dev)
+        opt = flat = None
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    if fused and float(ok) == 0.0:              # every rank switches together
+        fused = False
+        K = int(os.environ.get("B200MT_SHARDED_CHUNKS", "8"))
+        opt, flat = make(False, K)
     ggen = torch.Generator(device=dev).manual_seed(100 + rank)
     piece = 1 << 26
     for off in range(0, flat.numel(), piece):   # randn(seed = rank) in pieces (fp32 staging)

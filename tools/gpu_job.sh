@@ -1,3 +1,2 @@
-timeout 900 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo rc=$? >> gpurun_out/pytest_gpu.log
-tail -2 gpurun_out/pytest_gpu.log
-timeout 1200 python tools/bench_configs.py --out gpurun_out/configs.md > gpurun_out/configs.jsonl 2> gpurun_out/configs.err; echo rc=$?; tail -2 gpurun_out/configs.err; cut -c1-230 gpurun_out/configs.md
+timeout 900 python -m pytest tests/test_amp_more_gpu.py -m gpu -q > gpurun_out/pytest_amp_more.log 2>&1; echo rc=$? >> gpurun_out/pytest_amp_more.log
+grep -E "^E  |passed|failed|Error|^tests.*(Error|assert)" gpurun_out/pytest_amp_more.log | head -30
