@@ -585,6 +585,41 @@ __device__ __forceinline__ float bias_correction_dev(float beta, int step) {
   return __shfl_sync(0xffffffffu, r, 0);
 }
 
+// Division / square root of the update rules.  ncu on the mixed-precision Adam and LAMB kernels showed ~120
+// executed instructions per element with IEEE `div.rn` / `sqrt.rn` (each expands to a Newton sequence plus a
+// slow path for special values), enough to make those kernels issue-bound rather than HBM-bound.  The approximate
+// forms (MUFU.RCP / MUFU.SQRT, <= 2 ulp) are what the reference itself computes with: it is built --use_fast_math
+// (setup.py:210).  B200MT_APPROX_MATH=0 restores the IEEE forms.
+#ifndef B200MT_APPROX_MATH
+#define B200MT_APPROX_MATH 1
+#endif
+__device__ __forceinline__ float fast_div(float a, float b) {
+#if B200MT_APPROX_MATH
+  return __fdividef(a, b);
+#else
+  return a / b;
+#endif
+}
+__device__ __forceinline__ float fast_sqrt(float a) {
+#if B200MT_APPROX_MATH
+  float r;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(a));
+  return r;
+#else
+  return sqrtf(a);
+#endif
+}
+// x / c for a divisor c that is constant over a tile: multiply by the reciprocal taken once
+__device__ __forceinline__ float div_const(float x, float c, float rc) {
+#if B200MT_APPROX_MATH
+  (void)c;
+  return x * rc;
+#else
+  (void)rc;
+  return x / c;
+#endif
+}
+
 // Default no-op hooks an Op can inherit.
 struct OpBase {
   struct State {};

@@ -23,10 +23,10 @@ struct AdagradOp : OpBase {
     if (mode == 0) {
       g = g + decay * p;
       h = h + g * g;
-      p = p - lr * (g / (sqrtf(h) + eps));
+      p = p - lr * fast_div(g, fast_sqrt(h) + eps);
     } else {
       h = h + g * g;
-      p = p - lr * (g / (sqrtf(h) + eps) + decay * p);
+      p = p - lr * (fast_div(g, fast_sqrt(h) + eps) + decay * p);
     }
     x[1] = p; x[2] = h;
   }
@@ -76,23 +76,25 @@ struct NovoGradOp : OpBase {
   using Types = TypeList<T, T, T>;
   static constexpr unsigned STORES = 0b110;
   static constexpr int UNROLL = 2;
-  struct State { float denom; };
+  struct State { float denom, rdenom; };
   float beta1, beta3, bc1, bc2, eps, lr, decay;
   int moment_mode;
   const float* grad_norms;
   __device__ __forceinline__ unsigned load_mask() const { return 0b111; }
   __device__ __forceinline__ void tile_begin(State& s, const TileLoc& L) const {
     s.denom = grad_norms[L.tensor] / bc2 + eps;   // plain load: written by the kernel just before
+    s.rdenom = 1.f / s.denom;
   }
   __device__ __forceinline__ void elem(State& s, float (&x)[3]) const {
     float g = x[0], p = x[1], m = x[2];
+    const float rbc1 = 1.f / bc1;   // loop-invariant
     if (moment_mode == 0) {   // regularisation inside the moment
-      g = (g / s.denom) + (decay * p);
+      g = div_const(g, s.denom, s.rdenom) + (decay * p);
       m = beta1 * m + beta3 * g;
-      p = p - (lr * (m / bc1));
+      p = p - (lr * div_const(m, bc1, rbc1));
     } else {
       m = beta1 * m + beta3 * g;
-      const float update = ((m / bc1) / s.denom) + (decay * p);
+      const float update = div_const(div_const(m, bc1, rbc1), s.denom, s.rdenom) + (decay * p);
       p = p - (lr * update);
     }
     x[1] = p; x[2] = m;

@@ -47,19 +47,20 @@ struct AdamOp : OpBase {
   __device__ __forceinline__ unsigned load_mask() const { return 0b01111; }
   __device__ __forceinline__ void elem(State&, float (&x)[NL]) const {
     float g = x[0] * grad_scale, p = x[1], m = x[2], v = x[3];
+    const float rbc1 = 1.f / bc1, rbc2 = 1.f / bc2;   // loop-invariant: hoisted by the compiler
     if (mode == 0) {  // L2: decay folded into the gradient
       g = g + decay * p;
       m = beta1 * m + (1.f - beta1) * g;
       v = beta2 * v + (1.f - beta2) * g * g;
-      const float mu = m / bc1, vu = v / bc2;
-      const float denom = sqrtf(vu) + eps;
-      p = p - lr * (mu / denom);
+      const float mu = div_const(m, bc1, rbc1), vu = div_const(v, bc2, rbc2);
+      const float denom = fast_sqrt(vu) + eps;
+      p = p - lr * fast_div(mu, denom);
     } else {          // AdamW: decoupled decay
       m = beta1 * m + (1.f - beta1) * g;
       v = beta2 * v + (1.f - beta2) * g * g;
-      const float mu = m / bc1, vu = v / bc2;
-      const float denom = sqrtf(vu) + eps;
-      p = p - lr * (mu / denom + decay * p);
+      const float mu = div_const(m, bc1, rbc1), vu = div_const(v, bc2, rbc2);
+      const float denom = fast_sqrt(vu) + eps;
+      p = p - lr * (fast_div(mu, denom) + decay * p);
     }
     x[1] = p; x[2] = m; x[3] = v;
     if constexpr (COPY) x[4] = p;
@@ -79,7 +80,7 @@ struct DistAdamOp : OpBase {
   static constexpr int VEC = is_mc<Tg>::value ? B200MT_NVLS_VEC : B200MT_ADAM_VEC;
   static constexpr int THREADS = 256;
   static constexpr int MIN_CTAS = (VEC * UNROLL > 8) ? 2 : 4;
-  struct State { float b1, b2, eps, decay, bc1, bc2; };
+  struct State { float b1, b2, eps, decay, bc1, bc2, rbc1, rbc2, rgs; };
   const float *pt_beta1, *pt_beta2, *pt_eps, *pt_decay;
   const int* pt_bias_correction;
   float lr, grad_scale;
@@ -95,15 +96,16 @@ struct DistAdamOp : OpBase {
     } else {
       s.bc1 = 1.f; s.bc2 = 1.f;
     }
+    s.rbc1 = 1.f / s.bc1; s.rbc2 = 1.f / s.bc2; s.rgs = 1.f / grad_scale;
   }
   __device__ __forceinline__ void elem(State& s, float (&x)[NL]) const {
     float p = x[0], m = x[1], v = x[2];
-    const float g = x[3] / grad_scale;
+    const float g = div_const(x[3], grad_scale, s.rgs);
     m = s.b1 * m + (1.f - s.b1) * g;
     v = s.b2 * v + (1.f - s.b2) * g * g;
-    const float mu = m / s.bc1, vu = v / s.bc2;
-    const float denom = (mode == 0) ? sqrtf(vu + s.eps) : sqrtf(vu) + s.eps;
-    p = p - lr * (mu / denom + s.decay * p);
+    const float mu = div_const(m, s.bc1, s.rbc1), vu = div_const(v, s.bc2, s.rbc2);
+    const float denom = (mode == 0) ? fast_sqrt(vu + s.eps) : fast_sqrt(vu) + s.eps;
+    p = p - lr * (fast_div(mu, denom) + s.decay * p);
     x[0] = p; x[1] = m; x[2] = v;
     if constexpr (COPY) x[4] = p;
   }
@@ -126,11 +128,12 @@ struct ContribAdamOp : OpBase {
   __device__ __forceinline__ unsigned load_mask() const { return 0b01111; }
   __device__ __forceinline__ void elem(State&, float (&x)[NL]) const {
     float p = x[0], m = x[1], v = x[2];
-    const float g = x[3] / grad_scale;
+    const float rgs = 1.f / grad_scale;   // loop-invariant
+    const float g = div_const(x[3], grad_scale, rgs);
     m = b1 * m + (1.f - b1) * g;
     v = b2 * v + (1.f - b2) * g * g;
-    const float denom = (mode == 0) ? sqrtf(v + eps) : sqrtf(v) + eps;
-    const float update = (m / denom) + (decay * p);
+    const float denom = (mode == 0) ? fast_sqrt(v + eps) : fast_sqrt(v) + eps;
+    const float update = fast_div(m, denom) + (decay * p);
     p = p - (step_size * update);
     x[0] = p; x[1] = m; x[2] = v;
     if constexpr (COPY) x[4] = p;

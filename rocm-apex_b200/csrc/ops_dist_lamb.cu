@@ -21,7 +21,7 @@ struct DistLambStage1Op : OpBase {
   static constexpr int UNROLL = 1;
   static constexpr int THREADS = 256;
   static constexpr int MIN_CTAS = 4;
-  struct State { float combined_scale, b1, b2, b3, bc1, bc2, eps, decay, acc_u; int step; };
+  struct State { float combined_scale, rcs, b1, b2, b3, bc1, bc2, rbc1, rbc2, eps, decay, acc_u; int step; };
   const float *pt_beta1, *pt_beta2, *pt_eps, *pt_decay;
   const int* pt_bias_correction;
   const int* step_dev;
@@ -40,7 +40,7 @@ struct DistLambStage1Op : OpBase {
       cs = max_grad_norm / (*global_grad_norm / gs + 1e-6f);
       cs = gs / fminf(1.0f, cs);
     }
-    s.combined_scale = cs;
+    s.combined_scale = cs; s.rcs = 1.f / cs;
     s.step = *step_dev;
     s.acc_u = 0.f;
     return true;
@@ -57,20 +57,21 @@ struct DistLambStage1Op : OpBase {
     } else {
       s.bc1 = 1.f; s.bc2 = 1.f;
     }
+    s.rbc1 = 1.f / s.bc1; s.rbc2 = 1.f / s.bc2;
   }
   __device__ __forceinline__ void elem(State& s, float (&x)[NL]) const {
     const float p = (s.decay != 0.f) ? x[1] : 0.f;   // p is only used when decay != 0 (:192-203)
     float m = x[2], v = x[3], u;
-    float sg = x[0] / s.combined_scale;
+    float sg = div_const(x[0], s.combined_scale, s.rcs);
     if (mode == 0) {
       sg = sg + s.decay * p;
       m = m * s.b1 + s.b3 * sg;
       v = v * s.b2 + (1.f - s.b2) * sg * sg;
-      u = (m / s.bc1) / (sqrtf(v / s.bc2) + s.eps);
+      u = fast_div(div_const(m, s.bc1, s.rbc1), fast_sqrt(div_const(v, s.bc2, s.rbc2)) + s.eps);
     } else {
       m = m * s.b1 + s.b3 * sg;
       v = v * s.b2 + (1.f - s.b2) * sg * sg;
-      u = (m / s.bc1) / (sqrtf(v / s.bc2) + s.eps) + s.decay * p;
+      u = fast_div(div_const(m, s.bc1, s.rbc1), fast_sqrt(div_const(v, s.bc2, s.rbc2)) + s.eps) + s.decay * p;
     }
     const float ur = Elem<Tu>::round_trip(u);
     s.acc_u += ur * ur;

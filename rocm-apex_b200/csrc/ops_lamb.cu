@@ -35,7 +35,7 @@ struct LambStage1Op : OpBase {
   static constexpr int VEC = B200MT_LAMB_VEC;
   static constexpr int THREADS = 256;
   static constexpr int MIN_CTAS = (VEC * UNROLL > 8) ? 2 : 4;
-  struct State { float clip, inv_scale, bc1, bc2, acc_p, acc_u; };
+  struct State { float clip, inv_scale, bc1, bc2, rclip, rbc1, rbc2, acc_p, acc_u; };
   float beta1, beta2, beta3, eps, decay;
   float bc1_host, bc2_host, max_norm_host;
   int mode, bias_correction, want_norms;
@@ -67,6 +67,7 @@ struct LambStage1Op : OpBase {
       s.inv_scale = 1.f;
       s.bc1 = bc1_host; s.bc2 = bc2_host;
     }
+    s.rclip = 1.f / s.clip; s.rbc1 = 1.f / s.bc1; s.rbc2 = 1.f / s.bc2;
     return true;
   }
   // p is needed by the math only when decay != 0 (csrc/multi_tensor_lamb.cu:101-102) and by the
@@ -80,18 +81,18 @@ struct LambStage1Op : OpBase {
     if constexpr (MP) g = g * s.inv_scale;
     float u;
     if (mode == 0) {  // L2 on the clipped gradient
-      float sg = g / s.clip;
+      float sg = div_const(g, s.clip, s.rclip);
       sg = sg + decay * p;
       m = m * beta1 + beta3 * sg;
       v = v * beta2 + (1.f - beta2) * sg * sg;
-      const float mu = m / s.bc1, vu = v / s.bc2;
-      u = mu / (sqrtf(vu) + eps);
+      const float mu = div_const(m, s.bc1, s.rbc1), vu = div_const(v, s.bc2, s.rbc2);
+      u = fast_div(mu, fast_sqrt(vu) + eps);
     } else {          // decoupled decay
-      const float sg = g / s.clip;
+      const float sg = div_const(g, s.clip, s.rclip);
       m = m * beta1 + beta3 * sg;
       v = v * beta2 + (1.f - beta2) * sg * sg;
-      const float mu = m / s.bc1, vu = v / s.bc2;
-      u = mu / (sqrtf(vu) + eps) + decay * p;
+      const float mu = div_const(m, s.bc1, s.rbc1), vu = div_const(v, s.bc2, s.rbc2);
+      u = fast_div(mu, fast_sqrt(vu) + eps) + decay * p;
     }
     // the reference takes ||update|| over the values as stored in g's dtype
     const float ur = Elem<Tg>::round_trip(u);
@@ -164,12 +165,13 @@ struct LambSplitStage1Op : OpBase {
   __device__ __forceinline__ unsigned load_mask() const { return 0b01111u; }
   __device__ __forceinline__ void tile_begin(State& s, const TileLoc& L) const { s.decay = __ldg(per_tensor_decay + L.tensor); }
   __device__ __forceinline__ void elem(State& s, float (&x)[NL]) const {
-    const float sg = x[0] / clip;
+    const float rclip = 1.f / clip, rbc1 = 1.f / bc1, rbc2 = 1.f / bc2;   // loop-invariant
+    const float sg = div_const(x[0], clip, rclip);
     float m = x[2], v = x[3];
     m = m * beta1 + (1.f - beta1) * sg;
     v = v * beta2 + (1.f - beta2) * sg * sg;
-    const float mu = m / bc1, vu = v / bc2;
-    x[4] = mu / (sqrtf(vu) + eps) + s.decay * x[1];
+    const float mu = div_const(m, bc1, rbc1), vu = div_const(v, bc2, rbc2);
+    x[4] = fast_div(mu, fast_sqrt(vu) + eps) + s.decay * x[1];
     x[2] = m; x[3] = v;
   }
 };
