@@ -54,8 +54,9 @@ def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, str
         shard_elems = opt._layout["shard"]
         # per GPU and direction: out = my whole gradient buffer pulled by the switch (2*total) + my shard's
         # parameters sent once (2*shard); in = my shard's reduced gradients (2*shard) + everybody's parameters (2*total)
-        nv_bytes = 2.0 * total + 2.0 * shard_elems
-        kbytes = 28.0 * shard_elems
+        pbytes = 1.0 if opt._e5m2 else 2.0     # bytes per parameter in the broadcast
+        nv_bytes = 2.0 * total + pbytes * shard_elems          # the busier (outgoing) direction
+        kbytes = (26.0 + pbytes) * shard_elems
         achieved = kbytes / (ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": nparams / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -65,6 +66,7 @@ def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, str
                                    "bf16 grads reduced in the switch on load (multimem.ld_reduce), fused AdamW (fp32 master/moments), "
                                    "bf16 params broadcast by the switch on store (multimem.st)" % model_name,
                        "tensors": len(shapes), "params": nparams, "flat_elems": total, "parallelism": "zero-dp%d" % world,
+                       "e5m2_allgather": bool(opt._e5m2),
                        "l2": "inputs larger than L2 (%.1f GB of optimizer state per rank)" % (12.0 * shard_elems / 1e9)},
             "roofline": {"bound": "nvlink", "achieved": nv_bytes / (ms * 1e-3) / 1e9, "peak": NVLINK_GBS, "unit": "GB/s",
                          "frac": nv_bytes / (ms * 1e-3) / 1e9 / NVLINK_GBS, "traffic": None,
@@ -109,10 +111,14 @@ def run_sharded(args):
     params = []
     for s in shapes:
         params.append(torch.nn.Parameter((torch.randn(s, generator=gen, device=dev, dtype=torch.float32) * 0.02).to(torch.bfloat16)))
+    # B200MT_SHARDED_E5M2=1 (not the headline): the reference's e5m2_allgather=True -- parameters travel as one byte
+    # each and are unpacked into the bf16 model parameters by one extra maybe_cast_mt launch (no zero-copy then)
+    e5m2 = os.environ.get("B200MT_SHARDED_E5M2", "0") == "1"
+
     def make(fused_flag, chunks):
         o = DistributedFusedAdam(params, lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1, dwu_num_blocks=chunks,
-                                 dwu_num_chunks=1, predivide=False, overlap_reductions=False, zero_copy_params=True,
-                                 fused_collectives=fused_flag)
+                                 dwu_num_chunks=1, predivide=False, overlap_reductions=False, zero_copy_params=not e5m2,
+                                 fused_collectives=fused_flag, e5m2_allgather=e5m2)
         o.set_global_scale(float(world))        # gradients are summed by the reduce-scatter; the kernel divides by W
         return o, o.attach_flat_grads()
 
@@ -225,9 +231,11 @@ def run_sharded(args):
     if rank == 0:
         peak, peak_src = peaks()
         total = opt._layout["total"]
-        kbytes = 28.0 * shard_elems
+        pbytes = 1.0 if opt._e5m2 else 2.0
+        kbytes = (26.0 + pbytes) * shard_elems
         achieved = kbytes / (kernel_ms * 1e-3) / 1e9
-        nv_bytes = 2.0 * total * (world - 1) / world            # per direction per GPU, for each of RS and AG
+        nv_bytes = 2.0 * total * (world - 1) / world            # per direction per GPU, for the RS (the AG moves pbytes/2 of it)
+        ag_bytes = pbytes * total * (world - 1) / world
         line = {
             "metric": METRIC, "value": nparams / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -241,10 +249,10 @@ def run_sharded(args):
                          "kernel": "mt_stream_kernel<DistAdamOp<__nv_bfloat16,true>>", "bytes_per_launch": kbytes / K,
                          "avg_launch_ms": kernel_ms / K, "peak_source": peak_src},
             "nvlink": {"bytes_per_direction_per_gpu_per_collective": nv_bytes, "reduce_scatter_ms": rs_ms, "all_gather_ms": ag_ms,
-                       "reduce_scatter_gbs": nv_bytes / (rs_ms * 1e-3) / 1e9, "all_gather_gbs": nv_bytes / (ag_ms * 1e-3) / 1e9,
+                       "reduce_scatter_gbs": nv_bytes / (rs_ms * 1e-3) / 1e9, "all_gather_gbs": ag_bytes / (ag_ms * 1e-3) / 1e9,
                        "peak_gbs": NVLINK_GBS, "frac_rs": nv_bytes / (rs_ms * 1e-3) / 1e9 / NVLINK_GBS,
-                       "frac_ag": nv_bytes / (ag_ms * 1e-3) / 1e9 / NVLINK_GBS,
-                       "step_floor_ms": 2 * nv_bytes / (NVLINK_GBS * 1e9) * 1e3,
+                       "frac_ag": ag_bytes / (ag_ms * 1e-3) / 1e9 / NVLINK_GBS,
+                       "step_floor_ms": (nv_bytes + ag_bytes) / (NVLINK_GBS * 1e9) * 1e3, "e5m2_allgather": bool(opt._e5m2),
                        "overlap_efficiency": (rs_ms + ag_ms) / ms, "shard_kernel_ms": kernel_ms},
             "cpu_baseline": None,
             "e2e": {"value": nparams / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 2 * total * world, "d2h_bytes_per_step": 2 * world,

@@ -149,7 +149,12 @@ int b200mt_novograd(const b200mt_lists* lists, int chunk_size, int32_t* noop, fl
  *      (apex/contrib/csrc/optimizers/multi_tensor_distopt_adam_kernel.cu:169-228)
  * lists = [p32, m32, v32, g] or [p32, m32, v32, g, p_copy(g's dtype)].  Per-tensor device arrays
  * beta1/beta2/eps/weight_decay (float[ntensors]) and bias_correction (int32[ntensors]).
- * mode 0: eps inside sqrt, 1: outside. */
+ * mode 0: eps inside sqrt, 1: outside.
+ * p_copy may also be B200MT_U8: e5m2 bytes, the payload of the reference's `e5m2_allgather=True`
+ * (apex/contrib/optimizers/distributed_fused_adam.py:198,206), packed as fused_adam_cuda_kernel.cu:395-463
+ * packs them.  The reference's own kernel writes p_copy through a pointer of g's type whatever the buffer
+ * holds (multi_tensor_distopt_adam_kernel.cu:75-76,161), so this is the behaviour its Python side expects,
+ * not the one its kernel has. */
 int b200mt_dist_adam(const b200mt_lists* lists, int chunk_size, int32_t* noop,
                      const float* per_tensor_beta1, const float* per_tensor_beta2,
                      const int32_t* per_tensor_bias_correction, const float* per_tensor_eps,
@@ -185,8 +190,9 @@ int b200mt_dist_lamb_stage2(const b200mt_lists* lists, int chunk_size, int32_t* 
  * (NVLS) bound to the same symmetric buffers on every GPU of the NVSwitch domain, at this rank's shard.
  * The gradient load is multimem.ld_reduce (summed over all ranks inside the switch, fp32 accumulation),
  * the parameter store is multimem.st (replicated to all ranks by the switch): no separate collective.
- * dtype[3] == dtype[4] in {B200MT_F16, B200MT_BF16}; every fragment must be a multiple of 4 elements,
- * 8-byte (lists 3,4) / 16-byte (lists 0-2) aligned.  The caller brackets the launch with cross-GPU
+ * dtype[3] in {B200MT_F16, B200MT_BF16}; dtype[4] the same, or B200MT_U8 for an e5m2-compressed
+ * parameter broadcast (half the bytes through the switch).  Every fragment must be a multiple of 8
+ * elements; lists 0-2 32-byte, list 3 16-byte, list 4 16-byte (8-byte when e5m2) aligned.  The caller brackets the launch with cross-GPU
  * barriers (all ranks' gradients written before; all ranks' kernels finished after). */
 int b200mt_dist_adam_nvls(const b200mt_lists* lists, int chunk_size, int32_t* noop,
                           const float* per_tensor_beta1, const float* per_tensor_beta2,

@@ -86,8 +86,13 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         self._zero_copy_params = zero_copy_params
         if amsgrad:
             raise RuntimeError("DistributedFusedAdam does not support the AMSGrad variant.")
-        if e5m2_allgather:
-            raise NotImplementedError("e5m2-compressed all-gather is outside the hot path (SURVEY.md 8f-4)")
+        # e5m2_allgather (reference :64,198,206): the step kernel writes the parameter copy as e5m2 bytes,
+        # so the all-gather (or, fused, the multicast store) moves 1 byte per parameter instead of 2; the
+        # final maybe_cast_mt launch unpacks the bytes into the model parameters.
+        self._e5m2 = e5m2_allgather
+        if e5m2_allgather and zero_copy_params:
+            raise ValueError("zero_copy_params needs the gathered buffer in the parameter dtype; "
+                             "e5m2_allgather gathers bytes")
         super().__init__(params, dict(lr=lr, bias_correction=bias_correction, betas=betas, eps=eps,
                                       weight_decay=weight_decay, max_grad_norm=max_grad_norm))
         # kernels are looked up by module name, exactly as the reference does (:78-81)
@@ -147,11 +152,12 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         total, chunk, shard = L["total"], L["chunk"], L["shard"]
 
         self._overflow_buf = torch.zeros(1, dtype=torch.int32, device=dev)
+        gathered = torch.uint8 if self._e5m2 else low      # dtype that travels in the all-gather
         if self._fused:
             import torch.distributed._symmetric_memory as symm_mem
             assert self._cuda, "fused_collectives needs CUDA devices on one NVSwitch domain"
             self._flat_grads = symm_mem.empty(total, dtype=low, device=dev)
-            self._new_params = symm_mem.empty(total, dtype=low, device=dev)
+            self._new_params = symm_mem.empty(total, dtype=gathered, device=dev)
             self._flat_grads.zero_(); self._new_params.zero_()
             self._hdl_g = symm_mem.rendezvous(self._flat_grads, self._pg.group_name)
             self._hdl_p = symm_mem.rendezvous(self._new_params, self._pg.group_name)
@@ -160,10 +166,10 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                                    "this needs an NVSwitch domain with multicast support")
         else:
             self._flat_grads = torch.zeros(total, dtype=low, device=dev)      # RS input  [k][r][shard]
-            self._new_params = torch.zeros(total, dtype=low, device=dev)      # AG output [k][r][shard]
+            self._new_params = torch.zeros(total, dtype=gathered, device=dev) # AG output [k][r][shard]
         nlow = 0 if self._fused else K * shard                            # not materialised when fused
         self._fp16_g = torch.zeros(nlow, dtype=low, device=dev)           # RS output, this rank
-        self._fp16_p = torch.zeros(nlow, dtype=low, device=dev)           # Adam p_copy, AG input
+        self._fp16_p = torch.zeros(nlow, dtype=gathered, device=dev)      # Adam p_copy, AG input
         self._fp32_p = torch.zeros(K * shard, dtype=torch.float32, device=dev)
         self._fp32_m = torch.zeros(K * shard, dtype=torch.float32, device=dev)
         self._fp32_v = torch.zeros(K * shard, dtype=torch.float32, device=dev)
@@ -190,7 +196,8 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                     for lst, buf in zip(lists[:3], (self._fp32_p, self._fp32_m, self._fp32_v)):
                         lst.append(buf[base + soff:base + soff + n])
                     lists[3].append(RawBuffer(self._hdl_g.multicast_ptr + flat_pos * esize, n, low, dev))
-                    lists[4].append(RawBuffer(self._hdl_p.multicast_ptr + flat_pos * esize, n, low, dev))
+                    lists[4].append(RawBuffer(self._hdl_p.multicast_ptr + flat_pos * self._new_params.element_size(),
+                                              n, gathered, dev))
                 else:
                     sl = slice(base + soff, base + soff + n)
                     for lst, buf in zip(lists, (self._fp32_p, self._fp32_m, self._fp32_v, self._fp16_g, self._fp16_p)):

@@ -373,6 +373,32 @@ template <> struct Elem<mc_f16> {
   static __device__ __forceinline__ float round_trip(float v) { return __half2float(__float2half_rn(v)); }
 };
 
+// Store-only multicast view of an e5m2 byte list (the compressed all-gather of the sharded Adam):
+// 4 or 8 packed bytes per multimem.st, replicated by the switch.
+struct mc_e5m2 {};
+
+template <> struct Elem<mc_e5m2> {
+  static constexpr int SIZE = 1, QUAD_ALIGN = 4;
+  static __device__ __forceinline__ void ld4(const void*, float (&)[4]) { __trap(); }
+  static __device__ __forceinline__ void ld8(const void*, float (&)[8]) { __trap(); }
+  static __device__ __forceinline__ void st4(void* p, const float (&r)[4]) {
+    unsigned v = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) v |= f_to_e5m2(r[i]) << (8 * i);
+    asm volatile("multimem.st.relaxed.sys.global.b32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+  }
+  static __device__ __forceinline__ void st8(void* p, const float (&r)[8]) {
+    unsigned lo = 0, hi = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) { lo |= f_to_e5m2(r[i]) << (8 * i); hi |= f_to_e5m2(r[4 + i]) << (8 * i); }
+    const unsigned long long v = ((unsigned long long)hi << 32) | lo;
+    asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+  }
+  static __device__ __forceinline__ float ld1(const void*) { __trap(); return 0.f; }
+  static __device__ __forceinline__ void st1(void*, float) { __trap(); }
+  static __device__ __forceinline__ float round_trip(float v) { return e5m2_to_f(f_to_e5m2(v)); }
+};
+
 // vector access of V = 4 or 8 elements
 template <typename T, int V> __device__ __forceinline__ void ldv(const void* p, float (&r)[V]) {
   static_assert(V == 4 || V == 8, "vector width");

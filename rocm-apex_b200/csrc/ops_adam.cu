@@ -32,7 +32,7 @@ template <> struct is_mc<mc_f16> { static constexpr bool value = true; };
 
 // ---- amp_C.multi_tensor_adam ------------------------------------------------------------------
 // lists [g, p, m, v] (+ optional p_copy).  Per-element math follows
-// csrc/multi_tensor_adam.cu:94-112 in fp32 with IEEE division / sqrt.
+// csrc/multi_tensor_adam.cu:94-112 in fp32 (division / sqrt: see fast_div in mt_device.cuh).
 template <typename Tg, typename Tp, typename Tc, bool COPY>
 struct AdamOp : OpBase {
   using Types = typename std::conditional<COPY, TypeList<Tg, Tp, Tp, Tp, Tc>, TypeList<Tg, Tp, Tp, Tp>>::type;
@@ -68,12 +68,13 @@ struct AdamOp : OpBase {
 };
 
 // ---- distributed_adam_cuda.multi_tensor_fused_adam ---------------------------------------------
-// lists [p32, m32, v32, g] (+ p_copy in g's dtype); per-tensor hyper-parameters in device arrays;
-// bias correction evaluated on the device per tile from `step`
+// lists [p32, m32, v32, g] (+ p_copy in g's dtype, or e5m2 bytes for the compressed all-gather:
+// apex/contrib/optimizers/distributed_fused_adam.py:198,206); per-tensor hyper-parameters in device
+// arrays; bias correction evaluated on the device per tile from `step`
 // (multi_tensor_distopt_adam_kernel.cu:54-63,103-116).
-template <typename Tg, bool COPY>
+template <typename Tg, typename Tc, bool COPY>
 struct DistAdamOp : OpBase {
-  using Types = typename std::conditional<COPY, TypeList<float, float, float, Tg, Tg>, TypeList<float, float, float, Tg>>::type;
+  using Types = typename std::conditional<COPY, TypeList<float, float, float, Tg, Tc>, TypeList<float, float, float, Tg>>::type;
   static constexpr int NL = COPY ? 5 : 4;
   static constexpr unsigned STORES = COPY ? 0b10111 : 0b00111;
   static constexpr int UNROLL = is_mc<Tg>::value ? B200MT_NVLS_UNROLL : B200MT_ADAM_UNROLL;
@@ -210,7 +211,8 @@ extern "C" int b200mt_dist_adam(const b200mt_lists* L, int chunk_size, int32_t* 
   if (acquire_table(L, 4, 5, elementwise_tiling(), stream, &tv)) return 1;
   B200MT_CHECK(L->dtype[0] == B200MT_F32 && L->dtype[1] == B200MT_F32 && L->dtype[2] == B200MT_F32,
                "dist_adam: p, m, v must be fp32");
-  B200MT_CHECK(L->depth == 4 || L->dtype[4] == L->dtype[3], "dist_adam: p_copy must have the gradient dtype");
+  B200MT_CHECK(L->depth == 4 || L->dtype[4] == L->dtype[3] || L->dtype[4] == B200MT_U8,
+               "dist_adam: p_copy must have the gradient dtype or be e5m2 bytes");
   auto fill = [&](auto& op) {
     op.pt_beta1 = pt_beta1; op.pt_beta2 = pt_beta2; op.pt_eps = pt_eps; op.pt_decay = pt_weight_decay;
     op.pt_bias_correction = pt_bias_correction; op.lr = lr; op.grad_scale = grad_scale;
@@ -218,8 +220,9 @@ extern "C" int b200mt_dist_adam(const b200mt_lists* L, int chunk_size, int32_t* 
   };
   return dispatch_f32_f16_bf16(L->dtype[3], "dist_adam_cuda_kernel", [&](auto tg) {
     using Tg = typename decltype(tg)::type;
-    if (L->depth == 5) { DistAdamOp<Tg, true> op; fill(op); return launch_stream(tv, op, stream); }
-    DistAdamOp<Tg, false> op; fill(op);
+    if (L->depth == 5 && L->dtype[4] == B200MT_U8) { DistAdamOp<Tg, e5m2, true> op; fill(op); return launch_stream(tv, op, stream); }
+    if (L->depth == 5) { DistAdamOp<Tg, Tg, true> op; fill(op); return launch_stream(tv, op, stream); }
+    DistAdamOp<Tg, Tg, false> op; fill(op);
     return launch_stream(tv, op, stream);
   });
 }
@@ -239,13 +242,15 @@ extern "C" int b200mt_dist_adam_nvls(const b200mt_lists* L, int chunk_size, int3
   B200MT_CHECK(L->depth == 5, "dist_adam_nvls: expected [p32, m32, v32, g_multicast, p_copy_multicast]");
   B200MT_CHECK(L->dtype[0] == B200MT_F32 && L->dtype[1] == B200MT_F32 && L->dtype[2] == B200MT_F32,
                "dist_adam_nvls: p, m, v must be fp32");
-  B200MT_CHECK(L->dtype[3] == L->dtype[4] && (L->dtype[3] == B200MT_BF16 || L->dtype[3] == B200MT_F16),
-               "dist_adam_nvls: g and p_copy must both be Half or both BFloat16");
+  B200MT_CHECK((L->dtype[3] == B200MT_BF16 || L->dtype[3] == B200MT_F16) &&
+               (L->dtype[4] == L->dtype[3] || L->dtype[4] == B200MT_U8),
+               "dist_adam_nvls: g must be Half or BFloat16 and p_copy the same type or e5m2 bytes");
+  const bool packed = L->dtype[4] == B200MT_U8;
   for (int t = 0; t < L->ntensors; t++) {
     B200MT_CHECK(L->numel[t] % B200MT_NVLS_VEC == 0, "dist_adam_nvls: fragment %d has %lld elements; multicast fragments "
                  "must be multiples of %d elements", t, (long long)L->numel[t], B200MT_NVLS_VEC);
     for (int d = 0; d < 5; d++) {
-      const int al = (d < 3 ? 4 : 2) * B200MT_NVLS_VEC;
+      const int al = (d < 3 ? 4 : (d == 4 && packed) ? 1 : 2) * B200MT_NVLS_VEC;
       B200MT_CHECK(((uintptr_t)L->ptrs[(size_t)d * L->ntensors + t]) % al == 0,
                    "dist_adam_nvls: list %d fragment %d is not %d-byte aligned", d, t, al);
     }
@@ -261,8 +266,9 @@ extern "C" int b200mt_dist_adam_nvls(const b200mt_lists* L, int chunk_size, int3
     op.step = step; op.mode = mode;
     return launch_stream(tv, op, stream);
   };
-  if (L->dtype[3] == B200MT_BF16) return run(DistAdamOp<mc_bf16, true>());
-  return run(DistAdamOp<mc_f16, true>());
+  if (L->dtype[3] == B200MT_BF16)
+    return packed ? run(DistAdamOp<mc_bf16, mc_e5m2, true>()) : run(DistAdamOp<mc_bf16, mc_bf16, true>());
+  return packed ? run(DistAdamOp<mc_f16, mc_e5m2, true>()) : run(DistAdamOp<mc_f16, mc_f16, true>());
 }
 
 extern "C" int b200mt_contrib_adam(const b200mt_lists* L, int chunk_size, int32_t* noop, float lr,

@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _worker(rank, world, port, K, zero_copy, fused, out):
+def _worker(rank, world, port, K, zero_copy, fused, out, e5m2=False):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     for p in (os.path.join(ROOT, "rocm-apex_b200"), ROOT):
         if p not in sys.path:
@@ -30,8 +30,9 @@ def _worker(rank, world, port, K, zero_copy, fused, out):
         params = [torch.nn.Parameter(t.to(dev).bfloat16()) for t in init]
         opt = DistributedFusedAdam(params, lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=0.01, dwu_num_blocks=K,
                                    dwu_num_chunks=1, compute_L2_grad_norm=not fused, overlap_reductions=False,
-                                   zero_copy_params=zero_copy, fused_collectives=fused)
+                                   zero_copy_params=zero_copy, fused_collectives=fused, e5m2_allgather=e5m2)
         opt.set_global_scale(8.0)
+        import fused_adam_cuda
         # unsharded check: our own mixed-precision multi_tensor_adam [g, p32, m32, v32, p_copy] on the averaged grads
         m32 = [t.to(dev).bfloat16().float() for t in init]
         mm = [torch.zeros_like(t) for t in m32]
@@ -52,6 +53,19 @@ def _worker(rank, world, port, K, zero_copy, fused, out):
             want_norm = torch.sqrt(sum((a.float() ** 2).sum() for a in avg))
             if not fused:
                 assert abs(opt.L2_grad_norm - float(want_norm)) <= 1e-3 * float(want_norm)
+            if e5m2:
+                # model parameters = e5m2 rounding of the fp32 masters (bytes travelled, maybe_cast_mt unpacked them)
+                assert opt._new_params.dtype == torch.uint8
+                for p, m in zip(params, m32):
+                    byts = torch.zeros(m.numel(), dtype=torch.uint8, device=dev)
+                    want = torch.zeros(m.numel(), dtype=torch.bfloat16, device=dev)
+                    fused_adam_cuda.maybe_cast_mt(65536, flag, [[m.reshape(-1)], [byts]])
+                    fused_adam_cuda.maybe_cast_mt(65536, flag, [[byts], [want]])
+                    a, b = p.detach().float().reshape(-1), want.float()
+                    assert bool(((p.detach().reshape(-1).to(torch.float16).view(torch.int16) & 0xFF) == 0).all())
+                    assert float((a == b).float().mean()) >= (0.98 if fused else 0.999), (it, rank)
+                    assert bool(((a - m.reshape(-1)).abs() <= 0.126 * m.reshape(-1).abs() + 3e-4).all())
+                continue
             for pi, (p, c) in enumerate(zip(params, pc)):
                 # bf16 parameters: bit-exact expected, one bf16 ulp allowed where NCCL's summation order differs
                 a, b = p.detach().float().reshape(-1), c.float().reshape(-1)
@@ -92,6 +106,22 @@ def test_sharded_adam_matches_unsharded_world2_nccl(K, zero_copy, fused):
     q = ctx.Queue()
     port = 29700 + K + (20 if fused else 0) + (40 if zero_copy else 0)
     procs = [ctx.Process(target=_worker, args=(r, 2, port, K, zero_copy, fused, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in results:
+        assert msg == "ok", "rank %d: %s" % (rank, msg)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("K,fused", [(2, False), (1, True)])
+def test_e5m2_allgather_world2_nccl(K, fused):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29780 + K + (20 if fused else 0)
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, K, False, fused, q, True)) for r in range(2)]
     for p in procs:
         p.start()
     results = [q.get(timeout=300) for _ in procs]

@@ -187,3 +187,58 @@ def test_e5m2_pack_unpack_matches_reference():
         ours.strided_check_finite(f, y, stride, 1)
         refm.strided_check_finite(rf, y, stride, 1)
         assert int(f) == int(rf) == expect
+
+
+def test_oracle_e5m2_is_pinned_by_the_reference_kernel():
+    """oracle.pack_e5m2 / unpack_e5m2 against the reference's own convert<> (fused_adam_cuda_kernel.cu:395-463) run
+    through its maybe_cast_mt: every one of the 65536 Half bit patterns, all 256 bytes, and fp32 values around
+    every rounding boundary."""
+    refm = load_ref("fused_adam_cuda_ref")
+    if refm is None:
+        pytest.skip("oracle/_ref/fused_adam_cuda_ref.so not built")
+    halves = torch.arange(65536, dtype=torch.int32).to(torch.int16).view(torch.float16).cuda()
+    out = torch.zeros(65536, dtype=torch.uint8, device="cuda")
+    refm.maybe_cast_mt(CHUNK, flag_tensor(0), [[halves], [out]])
+    want = O.pack_e5m2(halves.float().cpu().numpy())
+    assert np.array_equal(out.cpu().numpy(), want)
+    g = torch.Generator(device="cuda").manual_seed(61)
+    x = torch.randn(1 << 18, generator=g, device="cuda") * torch.exp2(torch.randint(-20, 18, (1 << 18,), generator=g, device="cuda").float())
+    x[:8] = torch.tensor([0.0, -0.0, float("inf"), -float("inf"), float("nan"), 65504.0, 61440.0, 6e-8], device="cuda")
+    out = torch.zeros(x.numel(), dtype=torch.uint8, device="cuda")
+    refm.maybe_cast_mt(CHUNK, flag_tensor(0), [[x], [out]])
+    assert np.array_equal(out.cpu().numpy(), O.pack_e5m2(x.cpu().numpy()))
+    b = torch.arange(256, dtype=torch.int32).to(torch.uint8).cuda()
+    f = torch.zeros(256, device="cuda")
+    refm.maybe_cast_mt(CHUNK, flag_tensor(0), [[b], [f]])
+    got, want = f.cpu().numpy(), O.unpack_e5m2(b.cpu().numpy())
+    assert np.array_equal(np.isnan(got), np.isnan(want)) and np.array_equal(np.nan_to_num(got), np.nan_to_num(want))
+
+
+@pytest.mark.parametrize("gdt", ["f16", "bf16"])
+def test_dist_adam_e5m2_copy(gdt):
+    """distributed_adam_cuda.multi_tensor_fused_adam with an e5m2 p_copy (the payload of e5m2_allgather=True,
+    distributed_fused_adam.py:198,206): p/m/v bit-identical to the run with a 16-bit copy, bytes bit-identical
+    to the oracle's packing of the fp32 result."""
+    import distributed_adam_cuda as ours
+    T = len(SIZES)
+    lists = rand_lists(SIZES, [torch.float32, torch.float32, torch.float32, DT[gdt]], 62, positive=(2,))
+    plain = [[t.clone() for t in l] for l in lists] + [[torch.zeros(n, dtype=DT[gdt], device="cuda") for n in SIZES]]
+    packed = [[t.clone() for t in l] for l in lists] + [[torch.zeros(n, dtype=torch.uint8, device="cuda") for n in SIZES]]
+    dev = "cuda"
+    b1, b2 = torch.full((T,), 0.9, device=dev), torch.full((T,), 0.999, device=dev)
+    eps, wd = torch.full((T,), 1e-8, device=dev), torch.linspace(0, 0.1, T, device=dev)
+    bc = torch.ones(T, dtype=torch.int32, device=dev)
+    for step in (1, 2):
+        ours.multi_tensor_fused_adam(CHUNK, flag_tensor(), plain, b1, b2, bc, eps, wd, 1e-2, 2.0, step, 1)
+        ours.multi_tensor_fused_adam(CHUNK, flag_tensor(), packed, b1, b2, bc, eps, wd, 1e-2, 2.0, step, 1)
+    for d in range(3):
+        assert all(torch.equal(a, b) for a, b in zip(plain[d], packed[d]))
+    for p, c in zip(packed[0], packed[4]):
+        assert np.array_equal(c.cpu().numpy(), O.pack_e5m2(p.cpu().numpy()))
+    # misaligned views (head peel + scalar tail) give the same bytes
+    base = [torch.zeros(n + 3, dtype=torch.uint8, device="cuda") for n in SIZES]
+    views = [b[3:] for b in base]
+    again = [[t.clone() for t in l] for l in lists] + [views]
+    for step in (1, 2):
+        ours.multi_tensor_fused_adam(CHUNK, flag_tensor(), again, b1, b2, bc, eps, wd, 1e-2, 2.0, step, 1)
+    assert all(torch.equal(a, b) for a, b in zip(views, packed[4]))

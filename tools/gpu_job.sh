@@ -1,6 +1,7 @@
 mkdir -p gpurun_out
-python tools/sweep_math.py > gpurun_out/math_approx.json 2> gpurun_out/math_approx.err; tail -1 gpurun_out/math_approx.json; tail -3 gpurun_out/math_approx.err
-B200MT_LIB=$PWD/rocm-apex_b200/libb200mt_ieee.so python tools/sweep_math.py > gpurun_out/math_ieee.json 2> gpurun_out/math_ieee.err; tail -1 gpurun_out/math_ieee.json; tail -3 gpurun_out/math_ieee.err
-python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; tail -5 gpurun_out/pytest_gpu.log
-python bench.py > gpurun_out/bench_math.log 2>&1; tail -1 gpurun_out/bench_math.log | python -c "
-import sys,json; d=json.loads(sys.stdin.readline()); print(d['value'], d['ms_per_step'], d['roofline']['frac'], d['mixed_precision_adam'], d['e2e']['value'])"
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu2.log 2>&1; tail -5 gpurun_out/pytest_gpu2.log
+N=$(nvidia-smi -L | wc -l)
+run() { python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $1 bench.py --gpus $N --steps 5 --warmup 3; }
+B200MT_SHARDED_E5M2=1 run 29811 > gpurun_out/sh_e5m2_fused_$N.log 2>&1; tail -1 gpurun_out/sh_e5m2_fused_$N.log | cut -c1-400
+B200MT_SHARDED_E5M2=1 B200MT_SHARDED_FUSED=0 run 29812 > gpurun_out/sh_e5m2_nccl_$N.log 2>&1; tail -1 gpurun_out/sh_e5m2_nccl_$N.log | cut -c1-400
+run 29813 > gpurun_out/sh_plain_fused_$N.log 2>&1; tail -1 gpurun_out/sh_plain_fused_$N.log | cut -c1-300
