@@ -66,6 +66,52 @@ def shard_fragments(layout, numels, rank):
     return out
 
 
+def reshard_state_dicts(state_dicts, numels, new_world_size, new_num_chunks, old_num_chunks=None):
+    """Checkpoint shards written by `state_dict()` on every rank of one job (list indexed by rank, each
+    {step, fp32_p, fp32_m, fp32_v}: reference :598-616) -> the shards of a job with another world size
+    and / or pipeline-chunk count.  The reference can only resume on the layout that wrote the files;
+    here a parameter has the same flat offset in every layout (build_layout), so resharding is a
+    re-slicing of the flat space.  Host-side tensor indexing only; one of p/m/v is in flight at a time.
+    `numels`: parameter sizes in optimizer order; `old_num_chunks` defaults to what the shard sizes imply."""
+    old_world = len(state_dicts)
+    steps = {int(sd["step"]) for sd in state_dicts}
+    if len(steps) != 1:
+        raise ValueError("shards come from different steps: %s" % sorted(steps))
+    shard_len = state_dicts[0]["fp32_p"].numel()
+    if old_num_chunks is None and "layout" in state_dicts[0]:
+        old_num_chunks = int(state_dicts[0]["layout"]["num_chunks"])
+        if int(state_dicts[0]["layout"]["world_size"]) != old_world:
+            raise ValueError("%d shards given, written by a job of %d ranks" % (old_world, state_dicts[0]["layout"]["world_size"]))
+    if old_num_chunks is None:
+        # K*shard == total/W and total is the smallest multiple of 256*K*W covering the parameters
+        fits = [k for k in range(1, 257) if build_layout(numels, old_world, k)["shard"] * k == shard_len]
+        if len(fits) != 1:
+            raise ValueError("shard length %d fits pipeline-chunk counts %s for these parameters: pass old_num_chunks "
+                             "(dwu_num_blocks * dwu_num_chunks of the job that wrote the shards)" % (shard_len, fits))
+        old_num_chunks = fits[0]
+    old = build_layout(numels, old_world, old_num_chunks)
+    if old["shard"] * old_num_chunks != shard_len:
+        raise ValueError("shard length %d does not match world size %d x %d chunks" % (shard_len, old_world, old_num_chunks))
+    new = build_layout(numels, new_world_size, new_num_chunks)
+    used = min(old["total"], new["total"])        # everything past the last parameter is padding (zeros)
+    out = [{"step": min(steps), "layout": {"world_size": new_world_size, "num_chunks": new_num_chunks}}
+           for _ in range(new_world_size)]
+    for key in ("fp32_p", "fp32_m", "fp32_v"):
+        full = torch.zeros(max(old["total"], new["total"]), dtype=torch.float32)
+        for r, sd in enumerate(state_dicts):
+            t = sd[key].detach().to("cpu", torch.float32).reshape(old_num_chunks, old["shard"])
+            for k in range(old_num_chunks):
+                lo = k * old["chunk"] + r * old["shard"]
+                full[lo:lo + old["shard"]] = t[k]
+        full[used:] = 0
+        for r in range(new_world_size):
+            pieces = [full[k * new["chunk"] + r * new["shard"]:k * new["chunk"] + (r + 1) * new["shard"]]
+                      for k in range(new_num_chunks)]
+            out[r][key] = torch.cat(pieces).clone()
+        del full
+    return out
+
+
 class DistributedFusedAdam(torch.optim.Optimizer):
     def __init__(self, params, lr=1e-3, bias_correction=True, betas=(0.9, 0.999), eps=1e-8,
                  eps_inside_sqrt=False, weight_decay=0., max_grad_norm=0., amsgrad=False, flat_mt=False,
@@ -122,6 +168,7 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         self._init_done = False
         self._resume_state = None
         self._reduced = False
+        self._last_step = False
 
         self._pg = current_process_group if current_process_group is not None else dist.group.WORLD
         self._world_size = dist.get_world_size(self._pg)
@@ -140,6 +187,12 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                     self._model_params.append(p)
                     self._group_of.append(gi)
         assert len(self._model_params) > 0, "no parameters to optimise"
+        if self._world_size > 1:
+            # every rank starts from the first rank's parameters (reference :144-145)
+            src = dist.get_global_rank(self._pg, 0)
+            for group in self.param_groups:
+                for p in group["params"]:
+                    dist.broadcast(p.data, src=src, group=self._pg)
         p0 = self._model_params[0]
         dev, low = p0.device, p0.dtype
         assert all(p.dtype == low and p.device == dev for p in self._model_params), \
@@ -233,6 +286,22 @@ class DistributedFusedAdam(torch.optim.Optimizer):
             self._comm_stream = torch.cuda.Stream(device=dev)
             self._rs_done = [torch.cuda.Event() for _ in range(K)]
             self._adam_done = [torch.cuda.Event() for _ in range(K)]
+        # overlapped reductions (reference :158-164,381-395,489-502): a hook per parameter marks its gradient
+        # as produced; pipeline chunks are flushed (flattened + reduce-scattered on the side stream) from the
+        # LAST chunk down, each as soon as every parameter that touches it has its gradient -- backward
+        # produces gradients roughly last parameter first, so the reductions hide behind the rest of backward.
+        # Every rank flushes chunks in the same order, which keeps the collectives matched.
+        self._chunk_params = []
+        for k in range(K):
+            lo, hi = k * chunk, (k + 1) * chunk
+            self._chunk_params.append([i for i, (o, n) in enumerate(zip(L["offsets"], numels)) if o < hi and o + n > lo])
+        self._grad_ready = [False] * len(numels)
+        self._grad_flat = [False] * len(numels)       # already scaled into the flat buffer this iteration
+        self._next_chunk = K - 1
+        self._hooks = []
+        if self._overlap_reductions and not self._fused:
+            for i, p in enumerate(self._model_params):
+                self._hooks.append(p.register_post_accumulate_grad_hook(lambda _p, i=i: self._on_grad(i)))
         self._init_done = True
 
     # ------------------------------------------------------------------------------------------
@@ -281,39 +350,69 @@ class DistributedFusedAdam(torch.optim.Optimizer):
             p.grad = v
         return self._flat_grads
 
-    def _launch_reduce_scatters(self):
-        K, W, shard = self._num_chunks_total, self._world_size, self._layout["shard"]
-        chunk = self._layout["chunk"]
-        for k in range(K):
-            dist.reduce_scatter_tensor(self._fp16_g[k * shard:(k + 1) * shard],
-                                       self._flat_grads[k * chunk:(k + 1) * chunk], group=self._pg)
-            if self._cuda:
-                self._rs_done[k].record(torch.cuda.current_stream(self._device))
+    def set_last_step(self, last_step):
+        """While set, gradient hooks do not start reductions; complete_reductions() does all of them
+        (reference :378-379,496,556-569)."""
+        self._last_step = last_step
+
+    def _reduce_scatter_chunk(self, k):
+        shard, chunk = self._layout["shard"], self._layout["chunk"]
+        dist.reduce_scatter_tensor(self._fp16_g[k * shard:(k + 1) * shard],
+                                   self._flat_grads[k * chunk:(k + 1) * chunk], group=self._pg)
+        if self._cuda:
+            self._rs_done[k].record(torch.cuda.current_stream(self._device))
+
+    def _flush_chunks(self, chunks, final):
+        """Flatten (predivide + copy, ONE launch) the not yet flattened gradients of every parameter touching
+        `chunks`, then reduce-scatter those chunks on the communication stream.  `final`: parameters without a
+        gradient are treated as unused (zero), as complete_reductions() does in the reference (:556-564)."""
+        scale = 1.0 / self._world_size if self._predivide else 1.0
+        src, dst, inplace = [], [], []
+        for k in chunks:
+            for i in self._chunk_params[k]:
+                if self._grad_flat[i]:
+                    continue
+                p, v = self._model_params[i], self._grad_views[i]
+                if p.grad is None:
+                    assert final
+                    v.zero_()
+                elif p.grad.data_ptr() != v.data_ptr():
+                    src.append(p.grad); dst.append(v)
+                elif scale != 1.0:
+                    inplace.append(v)               # produced directly into the flat buffer (attach_flat_grads)
+                self._grad_flat[i] = True
+        if src or inplace:
+            multi_tensor_applier(self._multi_tensor_scale, self._overflow_buf, [src + inplace, dst + inplace], scale)
+        if self._fused:
+            return                                  # the reduction happens inside the step kernel
+        if self._cuda:
+            self._comm_stream.wait_stream(torch.cuda.current_stream(self._device))
+            with torch.cuda.stream(self._comm_stream):
+                for k in chunks:
+                    self._reduce_scatter_chunk(k)
+        else:
+            for k in chunks:
+                self._reduce_scatter_chunk(k)
+
+    def _on_grad(self, i):
+        """Gradient hook of parameter i (reference _do_overlapped_reduction, :489-502)."""
+        self._grad_ready[i] = True
+        if self._last_step or not self._overlap_reductions:
+            return
+        while self._next_chunk >= 0 and all(self._grad_ready[j] for j in self._chunk_params[self._next_chunk]):
+            with torch.no_grad():
+                self._flush_chunks([self._next_chunk], final=False)
+            self._next_chunk -= 1
 
     def complete_reductions(self):
-        """Flatten the gradients (predivided by the world size) and start the per-chunk reduce-scatters
-        on the communication stream (reference :552-575)."""
+        """Flatten the gradients (predivided by the world size) and start the reduce-scatters of every
+        pipeline chunk the gradient hooks have not already flushed (reference :552-575)."""
         self._init_everything()
-        grads, views = [], []
-        for p, v in zip(self._model_params, self._grad_views):
-            if p.grad is None:
-                v.zero_()                       # parameter unused this iteration
-            elif p.grad.data_ptr() != v.data_ptr():
-                grads.append(p.grad); views.append(v)
-        scale = 1.0 / self._world_size if self._predivide else 1.0
-        if grads:
-            multi_tensor_applier(self._multi_tensor_scale, self._overflow_buf, [grads, views], scale)
-        elif scale != 1.0:
-            self._flat_grads.mul_(scale)        # grads were produced directly into the flat buffer
-        if self._fused:
-            pass                                # the reduction happens inside the step kernel
-        elif self._cuda:
-            cur = torch.cuda.current_stream(self._device)
-            self._comm_stream.wait_stream(cur)
-            with torch.cuda.stream(self._comm_stream):
-                self._launch_reduce_scatters()
-        else:
-            self._launch_reduce_scatters()
+        with torch.no_grad():
+            self._flush_chunks(list(range(self._next_chunk, -1, -1)), final=True)
+        self._next_chunk = self._num_chunks_total - 1
+        self._grad_ready = [False] * len(self._grad_ready)
+        self._grad_flat = [False] * len(self._grad_flat)
         self._L2_grad_norm, self._l2_sq = None, None
         if self._compute_L2_grad_norm:
             # the shard buffer is contiguous after the reductions: one norm + one scalar all-reduce (:421-441)
@@ -360,12 +459,13 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                                                 # and nobody is still reading this rank's gradients
         elif self._cuda:
             cur = torch.cuda.current_stream(self._device)
-            for k in range(K):                                  # Adam(k) as soon as RS(k) has landed
+            order = range(K - 1, -1, -1)                        # the order the reduce-scatters were issued in
+            for k in order:                                     # Adam(k) as soon as RS(k) has landed
                 cur.wait_event(self._rs_done[k])
                 self._adam_chunk(k, combined_scale)
                 self._adam_done[k].record(cur)
             with torch.cuda.stream(self._comm_stream):          # AG(k) behind Adam(k), on the comm stream
-                for k in range(K):
+                for k in order:
                     self._comm_stream.wait_event(self._adam_done[k])
                     dist.all_gather_into_tensor(self._new_params[k * chunk:(k + 1) * chunk],
                                                 self._fp16_p[k * shard:(k + 1) * shard], group=self._pg)
@@ -382,9 +482,11 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         return loss
 
     def state_dict(self):
-        """This rank's shard: {step, fp32_p, fp32_m, fp32_v} (reference :598-616)."""
+        """This rank's shard: {step, fp32_p, fp32_m, fp32_v} (reference :598-616), plus a `layout` entry
+        (world size, pipeline chunks) that load_state_dict ignores and reshard_state_dicts() reads."""
         self._init_everything()
-        return {"step": self._step, "fp32_p": self._fp32_p, "fp32_m": self._fp32_m, "fp32_v": self._fp32_v}
+        return {"step": self._step, "fp32_p": self._fp32_p, "fp32_m": self._fp32_m, "fp32_v": self._fp32_v,
+                "layout": {"world_size": self._world_size, "num_chunks": self._num_chunks_total}}
 
     def load_state_dict(self, state_dict):
         if self._init_done:

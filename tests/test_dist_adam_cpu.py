@@ -193,6 +193,88 @@ def _worker_e5m2(rank, world, port, K, dtype_name, out):
         dist.destroy_process_group()
 
 
+def _worker_overlap(rank, world, port, K, dtype_name, out):
+    """overlap_reductions=True: gradient hooks flush pipeline chunks during backward, last chunk first
+    (reference :158-164,381-395,489-502); the result is bit-identical to reducing everything afterwards."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    for p in (os.path.join(ROOT, "rocm-apex_b200"), ROOT):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import apex  # noqa: F401
+        _install_kernel_doubles()
+        from apex.contrib.optimizers.distributed_fused_adam import DistributedFusedAdam
+        dtype = getattr(torch, dtype_name)
+        shapes = [(300, 7), (64,), (5,), (1000, 3), (1,), (700,)]
+        g0 = torch.Generator().manual_seed(7 + rank)             # ranks start differently: rank 0's values must win
+        init = [torch.randn(s, generator=g0) * 0.1 for s in shapes]
+        pa = [torch.nn.Parameter(t.to(dtype)) for t in init]
+        pb = [torch.nn.Parameter(t.to(dtype)) for t in init]
+        kw = dict(lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=0.01, dwu_num_blocks=K, dwu_num_chunks=1)
+        oa = DistributedFusedAdam(pa, overlap_reductions=True, **kw)
+        ob = DistributedFusedAdam(pb, overlap_reductions=False, **kw)
+        oa._init_everything(); ob._init_everything()             # hooks exist from the first backward on
+        first = [torch.zeros_like(p.data) for p in pa]
+        for f, p in zip(first, pa):
+            f.copy_(p.data)
+            dist.broadcast(f, src=0)
+            assert torch.equal(f, p.data)                        # every rank holds rank 0's parameters
+        assert len(oa._hooks) == len(pa) and len(ob._hooks) == 0
+        launched = []
+        orig = oa._reduce_scatter_chunk
+        oa._reduce_scatter_chunk = lambda k: (launched.append(k), orig(k))[1]
+        for it in range(4):
+            gr = torch.Generator().manual_seed(100 * it + rank)
+            xs = [torch.randn(s, generator=gr).to(dtype) for s in shapes]
+            skip = 1 if it == 2 else None                        # iteration 2: parameter 1 takes no part in the loss
+            last = it == 3                                       # iteration 3: set_last_step(True) -> no overlap
+            oa.set_last_step(last)
+            for params, opt in ((pa, oa), (pb, ob)):
+                for p in params:
+                    p.grad = None
+                loss = sum((p.float() * x.float()).sum() for i, (p, x) in enumerate(zip(params, xs)) if i != skip)
+                del launched[:]
+                loss.backward()
+                if opt is oa:
+                    if last:
+                        assert launched == [] and oa._next_chunk == K - 1
+                    elif skip is None:
+                        assert launched == list(range(K - 1, -1, -1)) and oa._next_chunk == -1
+                    else:
+                        # the chunk(s) holding parameter 1 and every chunk below stay pending
+                        k1 = min(k for k in range(K) if 1 in oa._chunk_params[k])
+                        assert oa._next_chunk >= k1 and launched == list(range(K - 1, oa._next_chunk, -1))
+                opt.complete_reductions()
+                if opt is oa:
+                    assert sorted(launched) == list(range(K)) and oa._next_chunk == K - 1
+                opt.step()
+            for a, b in zip(pa, pb):
+                assert torch.equal(a.detach(), b.detach()), (it, rank)
+            assert torch.equal(oa._fp32_p, ob._fp32_p) and torch.equal(oa._fp32_v, ob._fp32_v)
+        out.put((rank, "ok"))
+    except Exception:
+        import traceback
+        out.put((rank, "FAIL: " + traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("K,dtype_name", [(3, "float32"), (4, "bfloat16")])
+def test_overlapped_reductions_world2_gloo(K, dtype_name):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29660 + K
+    procs = [ctx.Process(target=_worker_overlap, args=(r, 2, port, K, dtype_name, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in results:
+        assert msg == "ok", "rank %d: %s" % (rank, msg)
+
+
 @pytest.mark.parametrize("K,dtype_name", [(2, "float16"), (1, "bfloat16")])
 def test_e5m2_allgather_world2_gloo(K, dtype_name):
     ctx = mp.get_context("spawn")

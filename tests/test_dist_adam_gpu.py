@@ -115,6 +115,66 @@ def test_sharded_adam_matches_unsharded_world2_nccl(K, zero_copy, fused):
         assert msg == "ok", "rank %d: %s" % (rank, msg)
 
 
+def _worker_overlap(rank, world, port, K, out):
+    """Reductions started by gradient hooks during a real backward pass (side stream, NCCL) give the same bits as
+    reducing everything in complete_reductions()."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    for p in (os.path.join(ROOT, "rocm-apex_b200"), ROOT):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        from apex.contrib.optimizers import DistributedFusedAdam
+        torch.manual_seed(11)
+        def net():
+            return torch.nn.Sequential(torch.nn.Linear(256, 512), torch.nn.GELU(), torch.nn.Linear(512, 512), torch.nn.GELU(),
+                                       torch.nn.Linear(512, 64)).to(dev).bfloat16()
+        ma = net()
+        mb = net()
+        mb.load_state_dict(ma.state_dict())
+        kw = dict(lr=1e-3, betas=(0.9, 0.99), eps=1e-8, weight_decay=0.01, dwu_num_blocks=K, dwu_num_chunks=1)
+        oa = DistributedFusedAdam(ma.parameters(), overlap_reductions=True, **kw)
+        ob = DistributedFusedAdam(mb.parameters(), overlap_reductions=False, **kw)
+        oa._init_everything(); ob._init_everything()
+        flushed_in_backward = 0
+        for it in range(4):
+            x = torch.randn(64, 256, generator=torch.Generator().manual_seed(100 * it + rank)).to(dev).bfloat16()
+            for model, opt in ((ma, oa), (mb, ob)):
+                for p in model.parameters():
+                    p.grad = None
+                model(x).float().pow(2).mean().backward()
+                if opt is oa:
+                    flushed_in_backward += (K - 1) - oa._next_chunk
+                opt.complete_reductions()
+                opt.step()
+            for a, b in zip(ma.parameters(), mb.parameters()):
+                assert torch.equal(a.detach(), b.detach()), (it, rank)
+        assert flushed_in_backward == 4 * K          # every chunk of every iteration left during backward
+        assert torch.equal(oa._fp32_p, ob._fp32_p) and torch.equal(oa._fp32_m, ob._fp32_m)
+        out.put((rank, "ok"))
+    except Exception:
+        import traceback
+        out.put((rank, "FAIL: " + traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_overlapped_reductions_world2_nccl():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_overlap, args=(r, 2, 29795, 4, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in results:
+        assert msg == "ok", "rank %d: %s" % (rank, msg)
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 @pytest.mark.parametrize("K,fused", [(2, False), (1, True)])
 def test_e5m2_allgather_world2_nccl(K, fused):
