@@ -396,6 +396,8 @@ class DistributedFusedAdam(torch.optim.Optimizer):
 
     def _on_grad(self, i):
         """Gradient hook of parameter i (reference _do_overlapped_reduction, :489-502)."""
+        if getattr(self, "_is_accumulation_step", False):   # DistributedFusedLAMB: nothing leaves until the last micro-batch
+            return
         self._grad_ready[i] = True
         if self._last_step or not self._overlap_reductions:
             return

@@ -96,7 +96,11 @@ class DistributedFusedLAMB(DistributedFusedAdam):
         self._one = torch.ones(1, dtype=torch.int32, device=dev)
         # the all-gather input must hold the current parameters from the start: a first step that overflows
         # skips update_weights and gathers whatever is in this buffer
-        self._fp16_p.copy_(self._fp32_p)
+        if self._e5m2:      # bytes: pack, do not convert numerically
+            multi_tensor_applier(self._contrib.maybe_cast_mt, torch.zeros_like(self._overflow_buf),
+                                 [[self._fp32_p], [self._fp16_p]])
+        else:
+            self._fp16_p.copy_(self._fp32_p)
         self._L2_grad_norm = None
         self._lamb_ready = True
 

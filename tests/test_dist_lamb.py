@@ -132,10 +132,68 @@ def _worker(rank, world, port, backend, out):
         dist.destroy_process_group()
 
 
-def _run(backend, port):
+def _worker_e5m2(rank, world, port, backend, out):
+    """e5m2_allgather=True next to a plain optimizer: an overflowing first step gathers the packed initial
+    parameters, the first clean step leaves bit-identical fp32 shards, and the model parameters are the e5m2
+    rounding of the masters (reference distributed_fused_lamb.py:203-206,850-861)."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    _paths()
+    cuda = backend == "nccl"
+    dev = torch.device("cuda", rank) if cuda else torch.device("cpu")
+    if cuda:
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    else:
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import apex  # noqa: F401
+        if not cuda:
+            _install_cpu_doubles()
+        from apex.contrib.optimizers import DistributedFusedLAMB
+        from oracle import mt_oracle as O
+        g0 = torch.Generator().manual_seed(11)
+        init = [torch.randn(s, generator=g0) * 0.1 for s in SHAPES]
+        pa = [torch.nn.Parameter(t.clone().to(dev).half()) for t in init]
+        pb = [torch.nn.Parameter(t.clone().to(dev).half()) for t in init]
+        kw = dict(lr=1e-2, betas=(0.9, 0.99), eps=1e-6, weight_decay=0.01, max_grad_norm=1.0, overlap_reductions=False)
+        oa, ob = DistributedFusedLAMB(pa, e5m2_allgather=True, **kw), DistributedFusedLAMB(pb, **kw)
+        for it in range(2):
+            gr = torch.Generator().manual_seed(100 * it + rank)
+            grads = [(torch.randn(s, generator=gr) * 4.0).half() for s in SHAPES]
+            if it == 0 and rank == 1:
+                grads[2][0] = float("inf")
+            for a, b, g in zip(pa, pb, grads):
+                a.grad, b.grad = g.clone().to(dev), g.clone().to(dev)
+            for o in (oa, ob):
+                o.set_global_scale(4.0)
+                o.complete_reductions()
+                o.step()
+            assert oa._new_params.dtype == torch.uint8 and int(oa._overflow_buf) == int(ob._overflow_buf) == (1 if it == 0 else 0)
+            shard = oa._layout["shard"]
+            mine = oa._new_params[rank * shard:(rank + 1) * shard].cpu().numpy()
+            assert (mine == O.pack_e5m2(oa._fp32_p.cpu().numpy())).all()
+            if it == 0:      # skipped step: model parameters untouched, gathered bytes = packed initial parameters
+                for a, t in zip(pa, init):
+                    assert torch.equal(a.detach().cpu(), t.half())
+            else:
+                assert torch.equal(oa._fp32_p, ob._fp32_p) and torch.equal(oa._fp32_m, ob._fp32_m)
+                for a, b in zip(pa, pb):
+                    h = a.detach().view(torch.int16)
+                    assert bool(((h & 0xFF) == 0).all())
+                    d = (a.detach().float() - b.detach().float()).abs()
+                    assert bool((d <= 0.13 * b.detach().float().abs() + 2e-5).all())
+        out.put((rank, "ok"))
+    except Exception:
+        import traceback
+        out.put((rank, "FAIL: " + traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def _run(backend, port, worker=None):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, backend, q)) for r in range(2)]
+    procs = [ctx.Process(target=worker or _worker, args=(r, 2, port, backend, q)) for r in range(2)]
     for p in procs:
         p.start()
     results = [q.get(timeout=300) for _ in procs]
@@ -147,6 +205,16 @@ def _run(backend, port):
 
 def test_sharded_lamb_host_logic_world2_gloo():
     _run("gloo", 29750)
+
+
+def test_sharded_lamb_e5m2_allgather_world2_gloo():
+    _run("gloo", 29752, _worker_e5m2)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_sharded_lamb_e5m2_allgather_world2_nccl():
+    _run("nccl", 29753, _worker_e5m2)
 
 
 @pytest.mark.gpu
@@ -198,6 +266,11 @@ def test_dist_lamb_kernels_match_oracle():
                 if cdt != torch.uint8:
                     for a, b in zip(pc, cpc):
                         assert_close_rel(a, b, rtol=1e-3 if cdt == torch.float16 else 1e-6, scale="self", what="stage2 p_copy")
+                else:   # the bytes are the (reference-pinned) e5m2 packing of the kernel's own fp32 result
+                    from oracle import mt_oracle as O
+                    import numpy as np
+                    for a, b in zip(pc, p):
+                        assert np.array_equal(a.cpu().numpy(), O.pack_e5m2(b.cpu().numpy()))
             # gating: flag == 1 -> nothing moves
             keep = [[t.clone() for t in l] for l in lists]
             one = torch.ones(1, dtype=torch.int32, device="cuda")
