@@ -221,6 +221,22 @@ int b200mt_maybe_cast(const b200mt_lists* lists, int chunk_size, const int32_t* 
 int b200mt_strided_check_finite(int32_t* noop, const void* p, int dtype, int64_t numel,
                                 int stride, int clear_overflow_first, int device, void* stream);
 
+/* ---- fused_adam_cuda.reversible_adam / maybe_adam_undo
+ *      (apex/contrib/csrc/optimizers/fused_adam_cuda_kernel.cu:570-653,814-912 and :655-732,961-1040)
+ * reversible_adam lists = [p32, m32, v32, g] or [.., p_copy (g's dtype, or e5m2 bytes for 16-bit g)]: adam_mt's
+ *   update where g/grad_scale is finite; elsewhere the element is left alone and the first element of p_copy
+ *   is overwritten with +inf (found later by strided_check_finite).
+ * maybe_adam_undo lists = [p32, m32, v32, g]: the inverse of that step, applied when overflow_flag is NULL or
+ *   *overflow_flag != 0.  Every element is reverted; the reference's kernel only reverts elements 0 mod 4
+ *   (its index inside the ILP loop is `j_start + i*ILP`, :687-690) -- see csrc/ops_reversible.cu.
+ * The reference binds these for flat tensors; lists of one tensor reproduce that, longer lists are an extension. */
+int b200mt_reversible_adam(const b200mt_lists* lists, int chunk_size, float lr, float beta1, float beta2,
+                           float eps, float grad_scale, int step, int mode, int bias_correction,
+                           float decay, void* stream);
+int b200mt_maybe_adam_undo(const b200mt_lists* lists, int chunk_size, const int32_t* overflow_flag, float lr,
+                           float beta1, float beta2, float eps, float grad_scale, int step, int mode,
+                           int bias_correction, float decay, void* stream);
+
 /* ---- b200mt_l2norm_flat_noalloc -- no counterpart in the reference.
  * L2 norm of ONE flat device buffer (x, dtype, numel) with the same two-pass arithmetic and the same
  * per-chunk overflow flag as b200mt_l2norm, for hosts that cannot let this library allocate: a

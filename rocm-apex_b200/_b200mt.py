@@ -83,6 +83,10 @@ def _load():
         "b200mt_nvls_all_gather": (c_int, [LP, c_int, vp]),
         "b200mt_contrib_adam": (c_int, [LP, c_int, vp, c_float, c_float, c_float, c_float, c_float, c_int,
                                         c_int, c_int, c_float, vp]),
+        "b200mt_reversible_adam": (c_int, [LP, c_int, c_float, c_float, c_float, c_float, c_float, c_int, c_int, c_int,
+                                           c_float, vp]),
+        "b200mt_maybe_adam_undo": (c_int, [LP, c_int, vp, c_float, c_float, c_float, c_float, c_float, c_int, c_int,
+                                           c_int, c_float, vp]),
         "b200mt_maybe_cast": (c_int, [LP, c_int, vp, vp]),
         "b200mt_strided_check_finite": (c_int, [vp, vp, c_int, ctypes.c_int64, c_int, c_int, c_int, vp]),
         "b200mt_l2norm_flat_noalloc": (c_int, [vp, c_int, ctypes.c_int64, c_int, vp, vp, c_int, vp]),

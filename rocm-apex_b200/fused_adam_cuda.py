@@ -1,5 +1,5 @@
-"""Drop-in `fused_adam_cuda` (apex/contrib/csrc/optimizers/fused_adam_cuda.cpp:78-86), restricted to
-the entry points the sharded hot path uses: adam_mt, maybe_cast_mt, strided_check_finite."""
+"""Drop-in `fused_adam_cuda` (apex/contrib/csrc/optimizers/fused_adam_cuda.cpp:78-86), all eight
+entry points: adam / adam_mt, reversible_adam, maybe_adam_undo, maybe_cast / maybe_cast_mt, strided_check_finite."""
 import torch
 
 import _b200mt as _mt
@@ -38,12 +38,6 @@ def strided_check_finite(overflow_flag, p_copy, stride, clear_overflow_first):
                                                int(clear_overflow_first), dev, _mt.stream_ptr(dev)))
 
 
-def _unsupported(name):
-    def f(*a, **k):
-        raise NotImplementedError("fused_adam_cuda.%s is outside the hot path (SURVEY.md 8f-4)" % name)
-    return f
-
-
 def adam(p, p_copy, m, v, g, lr, beta1, beta2, eps, grad_scale, step, mode, bias_correction, decay):
     """Flat-tensor form of adam_mt (fused_adam_cuda.cpp:27-38, fused_adam_cuda_kernel.cu:202-281): p_copy may be an
     empty tensor when no low-precision copy is wanted."""
@@ -65,8 +59,35 @@ def maybe_cast(overflow_flag, p_in, p_out):
     maybe_cast_mt(2048 * 32, overflow_flag, [[p_in], [p_out]])
 
 
-# reversible_adam / maybe_adam_undo stay out: besides being section 8f-4 material, the reference's undo kernel only
-# reverts every fourth element (`int j = j_start + i*ILP` inside the ILP loop, fused_adam_cuda_kernel.cu:687-690),
-# so there is no well-defined behaviour to be identical to.
-reversible_adam = _unsupported("reversible_adam")
-maybe_adam_undo = _unsupported("maybe_adam_undo")
+def _check_flat(p, m, v, g):
+    n = p.numel()
+    for name, t in (("m", m), ("v", v), ("g", g)):
+        if t.numel() != n:
+            raise RuntimeError("number of elements in %s and p tensors should be equal" % name)
+    return n
+
+
+def reversible_adam(p, p_copy, m, v, g, lr, beta1, beta2, eps, grad_scale, step, mode, bias_correction, decay):
+    """adam() applied only where g/grad_scale is finite; on overflow the elements concerned stay put and p_copy[0]
+    becomes +inf, to be found by strided_check_finite (fused_adam_cuda.cpp:43-55, fused_adam_cuda_kernel.cu:570-653).
+    An fp32 gradient writes no p_copy, like the reference (:897-899)."""
+    n = _check_flat(p, m, v, g)
+    if p_copy.numel() not in (0, n):
+        raise RuntimeError("number of elements in p_copy and p tensors should be equal, or p_copy should be empty")
+    lists = [[p], [m], [v], [g]] + ([[p_copy]] if (p_copy.numel() and g.dtype != torch.float32) else [])
+    L = _mt.pack(lists, (4, 5))
+    _mt.check(_lib.b200mt_reversible_adam(L.ref(), 2048 * 32, float(lr), float(beta1), float(beta2), float(eps),
+                                          float(grad_scale), int(step), int(mode), int(bias_correction), float(decay),
+                                          _mt.stream_ptr(L.device)))
+
+
+def maybe_adam_undo(overflow_flag, p, m, v, g, lr, beta1, beta2, eps, grad_scale, step, mode, bias_correction, decay):
+    """Inverse of reversible_adam's step, applied when the flag is set (or the flag tensor is empty)
+    (fused_adam_cuda.cpp:57-67, fused_adam_cuda_kernel.cu:655-732).  Reverts EVERY element; the reference's kernel
+    only reaches elements 0 mod 4 (see csrc/ops_reversible.cu)."""
+    _check_flat(p, m, v, g)
+    L = _mt.pack([[p], [m], [v], [g]], 4)
+    flag = _mt.noop_ptr(overflow_flag) if overflow_flag.numel() else None
+    _mt.check(_lib.b200mt_maybe_adam_undo(L.ref(), 2048 * 32, flag, float(lr), float(beta1), float(beta2), float(eps),
+                                          float(grad_scale), int(step), int(mode), int(bias_correction), float(decay),
+                                          _mt.stream_ptr(L.device)))
