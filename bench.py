@@ -267,13 +267,36 @@ def run_single(args):
         views.append(flat[off:off + n].view(s_))
         off += n
     e2e_steps = max(3, min(args.steps, 30))
+    # The copy is cut into E2E_SEGMENTS pieces on tensor boundaries, issued on a copy stream; the unscale + Adam
+    # launches of a piece follow its copy, so all but the last piece's compute hides under the PCIe transfer
+    # (tools/e2e_probe.py: copy alone 1.85 ms = 55 GB/s, unsegmented 2.01 ms, 4 segments 1.94 ms).
+    E2E_SEGMENTS = 4
+    numels = [p.numel() for p in params]
+    offs = [0]
+    for n in numels:
+        offs.append(offs[-1] + n)
+    bounds = [0]
+    for i in range(len(numels)):
+        if offs[i + 1] >= nparams * len(bounds) / E2E_SEGMENTS and len(bounds) < E2E_SEGMENTS:
+            bounds.append(i + 1)
+    bounds.append(len(numels))
+    copy_stream = torch.cuda.Stream(device=dev)
+    seg_ready = [torch.cuda.Event() for _ in range(len(bounds) - 1)]
 
     def e2e_step(k):
-        flat.copy_(host_grads, non_blocking=True)
         flag.zero_()
-        amp_C.multi_tensor_scale(CHUNK, flag, [views, views], inv_scale)
-        amp_C.multi_tensor_adam(CHUNK, flag, [views, params, m, v], ADAM["lr"], ADAM["beta1"], ADAM["beta2"],
-                                ADAM["eps"], k, 1, 1, ADAM["wd"])
+        copy_stream.wait_stream(stream)                  # the previous step is done with the gradient buffer
+        with torch.cuda.stream(copy_stream):
+            for s_ in range(len(bounds) - 1):
+                a, b = offs[bounds[s_]], offs[bounds[s_ + 1]]
+                flat[a:b].copy_(host_grads[a:b], non_blocking=True)
+                seg_ready[s_].record(copy_stream)
+        for s_ in range(len(bounds) - 1):
+            stream.wait_event(seg_ready[s_])
+            sl = slice(bounds[s_], bounds[s_ + 1])
+            amp_C.multi_tensor_scale(CHUNK, flag, [views[sl], views[sl]], inv_scale)
+            amp_C.multi_tensor_adam(CHUNK, flag, [views[sl], params[sl], m[sl], v[sl]], ADAM["lr"], ADAM["beta1"],
+                                    ADAM["beta2"], ADAM["eps"], k, 1, 1, ADAM["wd"])
         return flag.item()
 
     for k in range(3):
@@ -360,7 +383,9 @@ def run_single(args):
                          "host_cpus": cpu["host_cpus"], "ms_per_step": cpu["ms_per_step"]},
         "e2e": {"value": nparams / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 4 * nparams, "d2h_bytes_per_step": 4,
                 "ms_per_step": e2e_ms, "steps": e2e_steps,
-                "api": "amp_C.multi_tensor_scale + amp_C.multi_tensor_adam (drop-in entry points) + flag.item()"},
+                "segments": len(bounds) - 1, "pcie_floor_ms_at_55GBs": 4 * nparams / 55e9 * 1e3,
+                "api": "pinned-host gradients copied in %d segments on a copy stream; per segment amp_C.multi_tensor_scale + "
+                       "amp_C.multi_tensor_adam (drop-in entry points); flag.item() at the end" % (len(bounds) - 1)},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "mixed_precision_adam": {"what": "single-pass multi_tensor_adam [g fp16 (unscale fused), p/m/v fp32, p_copy fp16] on the same list, "
