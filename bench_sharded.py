@@ -20,9 +20,9 @@ NVLINK_GBS = 770.0     # measured peer-copy bandwidth per direction (B200_PROFIL
 
 
 def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, stream, flat, nparams, shapes, model_name, lib):
-    from bench import peaks, METRIC, UNIT
+    from bench import peaks, pinned_near_gpu, METRIC, UNIT
     clocks = sampler.stop() if rank == 0 else None
-    host = torch.empty(1 << 27, dtype=torch.bfloat16).pin_memory()
+    host = pinned_near_gpu(1 << 27, torch.bfloat16, local)
     host.normal_(0, 1)
     e2e_steps = max(2, min(args.steps, 5))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -202,7 +202,8 @@ def run_sharded(args):
 
     # e2e: the step's gradients arrive from pinned host memory (a 256 MiB pinned window copied repeatedly to
     # fill the flat buffer: pinning 16 GB per rank is not reasonable), the result read back is the gradient norm
-    host = torch.empty(1 << 27, dtype=torch.bfloat16).pin_memory()
+    from bench import pinned_near_gpu
+    host = pinned_near_gpu(1 << 27, torch.bfloat16, local)
     host.normal_(0, 1)
     e2e_steps = max(2, min(args.steps, 5))
 
