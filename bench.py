@@ -386,6 +386,32 @@ def run_single(args):
     torch.cuda.synchronize()
     mixed_ms = e0.elapsed_time(e1) / mixed_steps
 
+    # ---- the same two launches (+ flag clear) replayed from a CUDA graph: what is left of the step when the
+    # launch gaps go.  Auxiliary only: a captured multi_tensor_adam carries its host-side step number, so the bias
+    # correction does not advance between replays (the byte traffic and arithmetic are those of a real step).
+    graph_ms = None
+    try:
+        gs = torch.cuda.Stream(device=dev)
+        gs.wait_stream(stream)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=gs):
+            flag.zero_()
+            mt.check(lib.b200mt_scale(L_scale.ref(), CHUNK, fp, 1.0, gs.cuda_stream))
+            mt.check(lib.b200mt_adam(L_adam.ref(), CHUNK, fp, ADAM["lr"], ADAM["beta1"], ADAM["beta2"], ADAM["eps"],
+                                     1000, 1, 1, ADAM["wd"], 1.0, gs.cuda_stream))
+        stream.wait_stream(gs)
+        for _ in range(3):
+            graph.replay()
+        torch.cuda.synchronize()
+        e0.record(stream)
+        for _ in range(mixed_steps):
+            graph.replay()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        graph_ms = e0.elapsed_time(e1) / mixed_steps
+    except Exception as e:      # reported, not fatal: the headline numbers above do not depend on it
+        sys.stderr.write("bench: CUDA-graph leg failed: %r\n" % (e,))
+
     peak, peak_src = peaks()
     adam_bytes = 28.0 * nparams
     achieved = adam_bytes / (adam_avg * 1e-3) / 1e9
@@ -424,6 +450,9 @@ def run_single(args):
                                          "back-to-back launches", "ms_per_launch": mixed_ms, "value": nparams / (mixed_ms * 1e-3), "unit": UNIT,
                                  "achieved_gbs": 28.0 * nparams / (mixed_ms * 1e-3) / 1e9,
                                  "frac": 28.0 * nparams / (mixed_ms * 1e-3) / 1e9 / peak},
+        "cuda_graph_replay": {"ms_per_step": graph_ms, "value": (nparams / (graph_ms * 1e-3)) if graph_ms else None, "unit": UNIT,
+                              "what": "flag clear + b200mt_scale + b200mt_adam captured once with torch.cuda.graph and replayed "
+                                      "(auxiliary: the captured Adam keeps one step number)"},
         "python_api": {"value": nparams / (api_ms * 1e-3), "unit": UNIT, "ms_per_step": api_ms, "host_us_per_step": api_host_us,
                        "native_packer": mt._fast_pack is not None,
                        "what": "same resident step through amp_C.multi_tensor_scale + amp_C.multi_tensor_adam (2 x list packing per step)"},

@@ -103,17 +103,39 @@ struct Slot {
   cudaEvent_t uploaded = nullptr;
   std::vector<cudaStream_t> users;  // streams that may still be reading `dev`
   uint64_t tick = 0;
+  bool upload_done = false;  // the upload has been seen complete from the host: no stream needs to wait for it
+  bool pinned = false;       // used while a stream was capturing: a CUDA graph holds `dev`, never evict
 };
+
+constexpr uint32_t kMagic = 0xb200;   // first word of every table image
+constexpr size_t kAckBytes = 16;
+inline volatile uint32_t* slot_ack(Slot* s) {
+  return reinterpret_cast<volatile uint32_t*>(s->host + s->cap - kAckBytes);
+}
 
 struct StreamScratch { void* ptr = nullptr; size_t cap = 0; };
 
 struct DevCtx {
   Slot slots[kSlots];
   std::map<cudaStream_t, StreamScratch> scratch;
+  StreamScratch spare;          // zeroed, unassigned: handed to a stream first met while it is capturing
   std::vector<void*> retired;   // outgrown scratch buffers, possibly still in flight
   cudaEvent_t tmp_ev = nullptr;
   uint64_t tick = 0;
 };
+
+// Stream capture (CUDA graphs).  Nothing that allocates, synchronises or crosses the capture boundary may
+// run while `stream` is capturing, and everything a captured kernel points at must outlive the graph:
+//   * a list must have been seen once before the capture (its table is then resident and the upload is
+//     known complete); the slot is pinned so that the graph's table pointer stays valid;
+//   * scratch comes from the stream's own buffer if it has one, else from the pre-zeroed spare.
+// Violations are reported, never papered over.
+static int stream_is_capturing(cudaStream_t stream, bool* capturing) {
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  B200MT_CUDA(cudaStreamIsCapturing(stream, &st));
+  *capturing = st != cudaStreamCaptureStatusNone;
+  return 0;
+}
 
 DevCtx* g_ctx[kMaxDevices] = {nullptr};
 
@@ -207,22 +229,35 @@ int acquire_table(const b200mt_lists* L, int dmin, int dmax, const Tiling& tilin
     Slot& s = ctx->slots[i];
     if (s.valid && s.hash == hash && s.bytes == bytes && memcmp(s.host, img, bytes) == 0) { slot = &s; break; }
   }
+  bool capturing = false;
+  if (stream_is_capturing(stream, &capturing)) return 1;
   if (slot) {
     g_hits.fetch_add(1, std::memory_order_relaxed);
+    // the upload is followed by a 4-byte copy of the table's magic word back into pinned memory: seeing it there
+    // proves the upload is over without any CUDA call (none that queries or waits is safe while capturing)
+    if (!slot->upload_done && *slot_ack(slot) == kMagic) slot->upload_done = true;
     bool known = false;
     for (cudaStream_t u : slot->users) known = known || (u == stream);
-    if (!known) {  // first use on this stream: order after the upload
-      B200MT_CUDA(cudaStreamWaitEvent(stream, slot->uploaded, 0));
+    if (!known) {  // first use on this stream: order after the upload, unless it is known to be over
+      if (!slot->upload_done) {
+        B200MT_CHECK(!capturing, "stream capture: the upload of this tensor list's descriptor table is still in flight on "
+                                 "another stream; synchronise before capturing");
+        B200MT_CUDA(cudaStreamWaitEvent(stream, slot->uploaded, 0));
+      }
       slot->users.push_back(stream);
     }
+    if (capturing) slot->pinned = true;
   } else {
-    // evict the least recently used slot
-    slot = &ctx->slots[0];
+    B200MT_CHECK(!capturing, "stream capture: this tensor list has not been seen before the capture began; run the "
+                             "captured calls once (warm-up) with the same tensors first");
+    // evict the least recently used slot that no CUDA graph refers to
     for (int i = 0; i < kSlots; i++) {
       Slot& s = ctx->slots[i];
       if (!s.valid) { slot = &s; break; }
-      if (s.tick < slot->tick) slot = &s;
+      if (s.pinned) continue;
+      if (!slot || s.tick < slot->tick) slot = &s;
     }
+    B200MT_CHECK(slot != nullptr, "all %d descriptor-table slots of device %d are held by captured CUDA graphs", kSlots, L->device);
     if (!ctx->tmp_ev) B200MT_CUDA(cudaEventCreateWithFlags(&ctx->tmp_ev, cudaEventDisableTiming));
     if (!slot->uploaded) B200MT_CUDA(cudaEventCreateWithFlags(&slot->uploaded, cudaEventDisableTiming));
     if (slot->valid) {
@@ -236,20 +271,23 @@ int acquire_table(const b200mt_lists* L, int dmin, int dmax, const Tiling& tilin
       }
     }
     slot->valid = false;
+    slot->upload_done = false;
     slot->users.clear();
-    if (slot->cap < bytes) {
+    if (slot->cap < bytes + kAckBytes) {
       // Growing: the old device buffer may be read by kernels on this stream -> retire, don't free.
       if (slot->dev) ctx->retired.push_back(slot->dev);
       if (slot->host) cudaFreeHost(slot->host);
       slot->host = slot->dev = nullptr; slot->cap = 0;
       size_t cap = 16384;
-      while (cap < bytes) cap *= 2;
+      while (cap < bytes + kAckBytes) cap *= 2;     // the last kAckBytes of the pinned shadow hold the upload acknowledgement
       B200MT_CUDA(cudaHostAlloc((void**)&slot->host, cap, cudaHostAllocDefault));
       B200MT_CUDA(cudaMalloc((void**)&slot->dev, cap));
       slot->cap = cap;
     }
     memcpy(slot->host, img, bytes);
+    *slot_ack(slot) = 0;
     B200MT_CUDA(cudaMemcpyAsync(slot->dev, slot->host, bytes, cudaMemcpyHostToDevice, stream));
+    B200MT_CUDA(cudaMemcpyAsync(const_cast<uint32_t*>(slot_ack(slot)), slot->dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
     B200MT_CUDA(cudaEventRecord(slot->uploaded, stream));
     slot->hash = hash; slot->bytes = bytes; slot->valid = true;
     slot->users.push_back(stream);
@@ -272,8 +310,18 @@ int acquire_scratch(cudaStream_t stream, size_t bytes, void** out) {
   int device = 0;
   B200MT_CUDA(cudaGetDevice(&device));
   DevCtx* ctx = ctx_for_current_device(device);
+  bool capturing = false;
+  if (stream_is_capturing(stream, &capturing)) return 1;
   StreamScratch& s = ctx->scratch[stream];
-  if (s.cap < bytes) {
+  if (s.cap < bytes && capturing) {
+    // no allocation while capturing: adopt the spare (zeroed with a blocking memset when it was made)
+    B200MT_CHECK(ctx->spare.cap >= bytes, "stream capture: %zu bytes of scratch are needed on the capturing stream and none of "
+                 "that size exists yet; run the captured calls once before capturing (on the capture stream itself if the "
+                 "lists are larger than the warm-up's)", bytes);
+    if (s.ptr) ctx->retired.push_back(s.ptr);
+    s = ctx->spare;
+    ctx->spare = StreamScratch();
+  } else if (s.cap < bytes) {
     if (s.ptr) ctx->retired.push_back(s.ptr);  // may still be in flight on this stream
     size_t cap = 1 << 20;
     while (cap < bytes) cap *= 2;
@@ -281,6 +329,14 @@ int acquire_scratch(cudaStream_t stream, size_t bytes, void** out) {
     B200MT_CUDA(cudaMalloc(&s.ptr, cap));
     s.cap = cap;
     B200MT_CUDA(cudaMemsetAsync(s.ptr, 0, 256, stream));
+  }
+  if (!capturing && ctx->spare.cap < s.cap) {
+    // keep one unassigned buffer as large as the largest in use, for a stream that shows up already capturing
+    if (ctx->spare.ptr) ctx->retired.push_back(ctx->spare.ptr);
+    ctx->spare = StreamScratch();
+    B200MT_CUDA(cudaMalloc(&ctx->spare.ptr, s.cap));
+    ctx->spare.cap = s.cap;
+    B200MT_CUDA(cudaMemset(ctx->spare.ptr, 0, 256));
   }
   *out = s.ptr;
   return 0;
@@ -325,6 +381,7 @@ extern "C" int b200mt_shutdown(void) {
       if (s.uploaded) cudaEventDestroy(s.uploaded);
     }
     for (auto& kv : c->scratch) if (kv.second.ptr) cudaFree(kv.second.ptr);
+    if (c->spare.ptr) cudaFree(c->spare.ptr);
     for (void* p : c->retired) cudaFree(p);
     if (c->tmp_ev) cudaEventDestroy(c->tmp_ev);
     delete c;
