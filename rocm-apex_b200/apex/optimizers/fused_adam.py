@@ -21,6 +21,7 @@ class FusedAdam(torch.optim.Optimizer):
         amp_C = _common.require_extension("FusedAdam")
         self._dummy_overflow_buf = _common.overflow_buf()
         self.multi_tensor_adam = amp_C.multi_tensor_adam
+        self._lists = _common.GroupCache("FusedAdam", ("exp_avg", "exp_avg_sq"))
 
     def zero_grad(self, set_to_none=None):
         if self.set_grad_none if set_to_none is None else set_to_none:
@@ -36,25 +37,17 @@ class FusedAdam(torch.optim.Optimizer):
             raise RuntimeError("FusedAdam has been updated.  Simply initialize it identically to "
                                "torch.optim.Adam, and call step() with no arguments.")
         loss = closure() if closure is not None else None
-        for group in self.param_groups:
+        for gi, group in enumerate(self.param_groups):
             group["step"] = group.get("step", 0) + 1      # one counter per group, as in the reference
             beta1, beta2 = group["betas"]
-            entries = []
-            for p in group["params"]:
-                if p.grad is None:
-                    continue
-                if p.grad.is_sparse:
-                    raise RuntimeError("FusedAdam does not support sparse gradients, please consider SparseAdam instead")
-                if p.dtype not in _common.SUPPORTED:
-                    raise RuntimeError("FusedAdam only support fp16, bfloat16 and fp32.")
-                state = self.state[p]
-                if len(state) == 0:
-                    state["exp_avg"] = torch.zeros_like(p)
-                    state["exp_avg_sq"] = torch.zeros_like(p)
-                entries.append((p.grad, p, state["exp_avg"], state["exp_avg_sq"]))
-            for bucket in _common.by_dtype(entries):
-                lists = [list(col) for col in zip(*bucket)]
-                multi_tensor_applier(self.multi_tensor_adam, self._dummy_overflow_buf, lists, group["lr"],
+            # [g, p, exp_avg, exp_avg_sq] per dtype: the reference's per-parameter loop (:118-160), run once and memoised
+            for lists in self._lists.buckets(self, gi, group, self._init_state):
+                multi_tensor_applier(self.multi_tensor_adam, self._dummy_overflow_buf, list(lists), group["lr"],
                                      beta1, beta2, group["eps"], group["step"], self.adam_w_mode,
                                      1 if group["bias_correction"] else 0, group["weight_decay"])
         return loss
+
+    @staticmethod
+    def _init_state(p, state):
+        state["exp_avg"] = torch.zeros_like(p)
+        state["exp_avg_sq"] = torch.zeros_like(p)

@@ -22,6 +22,7 @@ class FusedLAMB(torch.optim.Optimizer):
         self.adam_w_mode = 1 if adam_w_mode else 0
         self.set_grad_none = set_grad_none
         self.use_nvlamb = use_nvlamb
+        self._lists = _common.GroupCache("FusedLAMB", ("exp_avg", "exp_avg_sq"))
 
     def zero_grad(self, set_to_none=None):
         if self.set_grad_none if set_to_none is None else set_to_none:
@@ -31,18 +32,20 @@ class FusedLAMB(torch.optim.Optimizer):
         else:
             super().zero_grad(set_to_none=False)
 
-    def _global_grad_norm(self):
+    @staticmethod
+    def _init_state(p, state):
+        state["exp_avg"] = torch.zeros_like(p)
+        state["exp_avg_sq"] = torch.zeros_like(p)
+
+    def _global_grad_norm(self, per_group):
         """sqrt(||g32||^2 + ||g16||^2 ...): one l2norm per dtype, then the l2norm of those norms
         (apex/optimizers/fused_lamb.py:107-136)."""
         device = self.param_groups[0]["params"][0].device
         grads = {}
-        for group in self.param_groups:
-            for p in group["params"]:
-                if p.grad is None:
-                    continue
-                if p.dtype not in _common.SUPPORTED:
-                    raise RuntimeError("FusedLAMB only support fp16, bfloat16 and fp32.")
-                grads.setdefault(p.dtype, []).append(p.grad)
+        for buckets in per_group:
+            for gs, ps, _, _ in buckets:
+                if gs:
+                    grads.setdefault(ps[0].dtype, []).extend(gs)
         norms = [multi_tensor_applier(self.multi_tensor_l2norm, self._dummy_overflow_buf, [g], False)[0]
                  for g in grads.values()]
         while len(norms) < 2:
@@ -52,25 +55,15 @@ class FusedLAMB(torch.optim.Optimizer):
     @torch.no_grad()
     def step(self, closure=None):
         loss = closure() if closure is not None else None
-        global_grad_norm = self._global_grad_norm()
+        # [g, p, exp_avg, exp_avg_sq] per group and dtype: the reference's per-parameter loops (:107-136,149-190), memoised
+        per_group = [self._lists.buckets(self, gi, group, self._init_state) for gi, group in enumerate(self.param_groups)]
+        global_grad_norm = self._global_grad_norm(per_group)
         max_grad_norm = self.defaults["max_grad_norm"]
-        for group in self.param_groups:
+        for group, buckets in zip(self.param_groups, per_group):
             group["step"] = group.get("step", 0) + 1
             beta1, beta2 = group["betas"]
-            entries = []
-            for p in group["params"]:
-                if p.grad is None:
-                    continue
-                if p.grad.is_sparse:
-                    raise RuntimeError("FusedLAMB does not support sparse gradients, please consider SparseAdam instead")
-                state = self.state[p]
-                if len(state) == 0:
-                    state["exp_avg"] = torch.zeros_like(p)
-                    state["exp_avg_sq"] = torch.zeros_like(p)
-                entries.append((p.grad, p, state["exp_avg"], state["exp_avg_sq"]))
-            for bucket in _common.by_dtype(entries):
-                lists = [list(col) for col in zip(*bucket)]
-                multi_tensor_applier(self.multi_tensor_lamb, self._dummy_overflow_buf, lists, group["lr"],
+            for lists in buckets:
+                multi_tensor_applier(self.multi_tensor_lamb, self._dummy_overflow_buf, list(lists), group["lr"],
                                      beta1, beta2, group["eps"], group["step"],
                                      1 if group["bias_correction"] else 0, group["weight_decay"],
                                      1 if group["grad_averaging"] else 0, self.adam_w_mode,

@@ -29,9 +29,11 @@ class FusedSGD(torch.optim.Optimizer):
         amp_C = _common.require_extension("FusedSGD")
         self._dummy_overflow_buf = _common.overflow_buf(self.param_groups[0]["params"][0].device)
         self.multi_tensor_sgd = amp_C.multi_tensor_sgd
+        self._sets = {}
 
     def __setstate__(self, state):
         super().__setstate__(state)
+        self._sets = {}
         for group in self.param_groups:
             group.setdefault("nesterov", False)
 
@@ -73,11 +75,43 @@ class FusedSGD(torch.optim.Optimizer):
             moms32, first32 = self.get_momentums(fp32_params)
             return [([grads, mparams, moms16, [models[i] for i in keep]], first16),
                     (fp32_set + [moms32], first32)]
-        sets = []
+        # The reference walks every parameter three times per step here (:182-199); once the momentum buffers exist
+        # the lists are memoised and a step only re-reads p.grad and checks by identity that nothing moved
+        # (see _common.GroupCache for the rules).
+        c = self._sets.get(gid)
+        if c is not None and c[0] is self.state and c[1] is group["params"] and c[2] == len(group["params"]):
+            sets = self._memoised_sets(c)
+            if sets is not None:
+                return sets
+        sets, rows_by_dt, all_warm = [], [], True
         for dt in (torch.float16, torch.float32):
             ps = [p for p in group["params"] if p.dtype == dt and p.grad is not None]
             moms, first = self.get_momentums(ps)
+            all_warm = all_warm and not (first and ps)
             sets.append(([[p.grad for p in ps], ps, moms], first))
+            rows_by_dt.append(([(p, self.state[p], m) for p, m in zip(ps, moms)], ps, moms))
+        if all_warm:
+            idle = [p for p in group["params"] if p.grad is None]
+            self._sets[gid] = (self.state, group["params"], len(group["params"]), idle, rows_by_dt)
+        else:
+            self._sets.pop(gid, None)
+        return sets
+
+    @staticmethod
+    def _memoised_sets(c):
+        for p in c[3]:
+            if p.grad is not None:
+                return None
+        sets = []
+        for rows, ps, moms in c[4]:
+            gs = []
+            add = gs.append
+            for p, st, mom in rows:
+                g = p.grad
+                if g is None or st.get("momentum_buffer") is not mom:
+                    return None
+                add(g)
+            sets.append(([gs, ps, moms], False))
         return sets
 
     @torch.no_grad()

@@ -1,0 +1,138 @@
+"""GPU: the memoised tensor lists of FusedAdam / FusedLAMB (apex/optimizers/_common.py: GroupCache) must notice everything
+the reference's per-step Python loop (apex/optimizers/fused_adam.py:118-160) would have seen: gradients appearing and
+disappearing, state loaded from a checkpoint, state tensors replaced by the user, parameter groups added, gradient
+tensors re-allocated every step.  FusedAdam is stepped next to torch.optim.AdamW in the steady state and next to an uncached twin through all of it."""
+import copy
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def make(n=6, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    shapes = [(33, 7), (128,), (5,), (64, 64), (1,), (1000,)][:n]
+    a = [torch.nn.Parameter(torch.randn(s, generator=g, device="cuda") * 0.1) for s in shapes]
+    b = [torch.nn.Parameter(p.detach().clone()) for p in a]
+    return a, b
+
+
+def set_grads(a, b, seed, skip=()):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    for i, (p, q) in enumerate(zip(a, b)):
+        gr = torch.randn(p.shape, generator=g, device="cuda")
+        if i in skip:
+            p.grad, q.grad = None, None
+        else:
+            p.grad, q.grad = gr.clone(), gr.clone()      # fresh tensors every step, like backward after zero_grad(set_to_none)
+
+
+def same(a, b, tol=2e-6):
+    return all(float((p.detach() - q.detach()).abs().max()) <= tol for p, q in zip(a, b))
+
+
+def test_fused_adam_cache_tracks_grads_state_and_groups():
+    from apex.optimizers import FusedAdam
+    a, b = make()
+    kw = dict(lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=0.01)
+    # steady state against torch.optim.AdamW first (same per-step counters as long as every parameter has a gradient)
+    x, y = make(seed=1)
+    fx, ty = FusedAdam(x, **kw), torch.optim.AdamW(y, **kw)
+    for it in range(4):
+        set_grads(x, y, it)
+        fx.step(); ty.step()
+        assert same(x, y)
+
+    class Uncached(FusedAdam):                            # the reference's loop on every step
+        def step(self, *args, **kwargs):
+            self._lists.clear()
+            return super().step(*args, **kwargs)
+
+    fa, ta = FusedAdam(a[:4], **kw), Uncached(b[:4], **kw)
+    hits = lambda: fa._lists.groups[0][4]
+    for it in range(3):                                   # cache built on step 0, reused after
+        set_grads(a, b, it)
+        fa.step(); ta.step()
+        assert same(a, b, tol=0.0)
+    rows_before = hits()
+    set_grads(a, b, 10)
+    fa.step(); ta.step()
+    assert hits() is rows_before and same(a, b)           # fast path really was taken
+    # a parameter without gradient this step, then with one again
+    set_grads(a, b, 11, skip=(1,))
+    fa.step(); ta.step()
+    assert same(a, b) and hits() is not rows_before
+    set_grads(a, b, 12)
+    fa.step(); ta.step()
+    assert same(a, b)
+    # a new parameter group
+    fa.add_param_group({"params": a[4:], "lr": 5e-3})
+    ta.add_param_group({"params": b[4:], "lr": 5e-3})
+    for it in range(2):
+        set_grads(a, b, 20 + it)
+        fa.step(); ta.step()
+        assert same(a, b)
+    # the user replaces a state tensor behind the optimizer's back
+    fa.state[a[0]]["exp_avg"] = torch.zeros_like(a[0])
+    ta.state[b[0]]["exp_avg"] = torch.zeros_like(b[0])
+    set_grads(a, b, 30)
+    fa.step(); ta.step()
+    assert same(a, b)
+    # checkpoint round trip into a fresh optimizer on cloned parameters, both continue identically
+    a2 = [torch.nn.Parameter(p.detach().clone()) for p in a]
+    fa2 = FusedAdam([{"params": a2[:4]}, {"params": a2[4:], "lr": 5e-3}], **kw)
+    set_grads(a2, a2, 0)
+    fa2.step()                                            # builds a cache that the load below must invalidate
+    with torch.no_grad():
+        for p, q in zip(a2, a):
+            p.copy_(q)
+    fa2.load_state_dict(copy.deepcopy(fa.state_dict()))
+    for it in range(2):
+        set_grads(a, b, 40 + it)
+        for p, q in zip(a2, a):
+            p.grad = q.grad.clone()
+        fa.step(); ta.step(); fa2.step()
+        assert same(a, b) and same(a2, a, tol=0.0)
+    # zero_grad(set_to_none) then a step with no gradients at all is a no-op
+    fa.zero_grad()
+    before = [p.detach().clone() for p in a]
+    fa.step()
+    assert all(torch.equal(x, p.detach()) for x, p in zip(before, a))
+
+
+def test_fused_lamb_cache_matches_uncached_steps():
+    from apex.optimizers import FusedLAMB
+    a, b = make()
+    kw = dict(lr=1e-2, weight_decay=0.01, max_grad_norm=1.0)
+    cached, fresh = FusedLAMB(a, **kw), FusedLAMB(b, **kw)
+    for it in range(5):
+        set_grads(a, b, it, skip=(2,) if it == 3 else ())
+        fresh._lists.clear()                              # always the slow pass: the reference's loop
+        cached.step(); fresh.step()
+        assert same(a, b, tol=0.0)
+    assert cached.param_groups[0]["step"] == 5
+
+
+def test_fused_sgd_memo_matches_uncached_steps_and_torch():
+    from apex.optimizers import FusedSGD
+    a, b = make()
+    c = [torch.nn.Parameter(p.detach().clone()) for p in a]
+    kw = dict(lr=1e-2, momentum=0.9, weight_decay=1e-4, nesterov=True)
+    cached, fresh, ref = FusedSGD(a, **kw), FusedSGD(b, **kw), torch.optim.SGD(c, **kw)
+    for it in range(6):
+        skip = (2,) if it == 3 else ()
+        set_grads(a, b, it, skip=skip)
+        for p, q in zip(c, a):
+            p.grad = None if q.grad is None else q.grad.clone()
+        fresh._sets.clear()                               # always the reference's three walks over the parameters
+        cached.step(); fresh.step(); ref.step()
+        assert same(a, b, tol=0.0) and same(a, c, tol=1e-6)
+        if it == 2:
+            assert 0 in cached._sets                      # memo in place once the momentum buffers exist
+    sd = copy.deepcopy(cached.state_dict())
+    cached.load_state_dict(sd)                            # state objects replaced: the memo must not survive
+    assert cached._sets == {}
+    set_grads(a, b, 50)
+    cached.step(); fresh._sets.clear(); fresh.step()
+    assert same(a, b, tol=0.0)
