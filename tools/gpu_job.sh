@@ -1,3 +1,3 @@
 mkdir -p gpurun_out
-python -m pytest tests/test_optimizer_cache_gpu.py tests/test_optimizers_gpu.py tests/test_amp_more_gpu.py -m gpu -x -q > gpurun_out/pytest_opt.log 2>&1; tail -12 gpurun_out/pytest_opt.log
-python tools/bench_optimizer_api.py 2>&1 | tail -1
+python tools/bench_configs.py --out gpurun_out/configs_final.md > gpurun_out/configs_final.jsonl 2> gpurun_out/configs_final.err; tail -3 gpurun_out/configs_final.err; wc -l gpurun_out/configs_final.md gpurun_out/configs_final.jsonl
+python tools/sweep_variants.py > gpurun_out/variants_final.json 2>&1; tail -1 gpurun_out/variants_final.json
