@@ -247,8 +247,8 @@ int b200mt_maybe_adam_undo(const b200mt_lists* lists, int chunk_size, const int3
  *   - B200MT_NOALLOC_SCRATCH_BYTES of device memory are held on every GPU that loads the library,
  *     until the process exits;
  *   - inputs that need more than B200MT_NOALLOC_MAX_TILES scheduling tiles are refused with an error
- *     (1,073,741,824 elements at the default 16384-element norm tile with chunk_size >= 16384; fewer
- *     for smaller chunk sizes -- at least one tile per chunk -- or a smaller B200MT_NORM_TILE_ELEMS);
+ *     (1,073,741,824 elements with chunk_size >= 16384: this entry point always tiles by 16384
+ *     elements; fewer for smaller chunk sizes -- at least one tile per chunk);
  *   - all calls on a device share the array: calls whose GPU work may overlap (unordered streams)
  *     race and must be ordered by the caller; back-to-back calls on one stream are safe, the
  *     function re-zeroes what has to start at zero;

@@ -21,9 +21,10 @@ static int g_tile_elems = 0;  // 0 = not yet initialised
 static int g_grid_cap = 0;    // 0 = one CTA per tile
 static bool g_pdl = true;     // programmatic dependent launch of the streaming kernels (B200MT_PDL=0 disables)
 // Kernels that end every tile with a CTA-wide reduction (l2norm, LAMB stage 1) want longer tiles than the
-// pure streaming ones: 16384 vs 4096 elements is 1.3x (fp32) to 1.8x (fp16) on l2norm and 1.16x on lamb_mp
-// (profiles/sweep_norm_r01.txt).
-static int g_norm_tile_elems = 16384;
+// pure streaming ones: 8192 vs 4096 elements is 1.3x on l2norm and 1.1x on lamb_mp (profiles/sweep_norm_r01.txt);
+// with the final kernels 8192 beats 16384 by 1-2 % on l2norm / LAMB and 5 % on 16-bit l2norm
+// (profiles/sweep_norm2_r01.txt).  16-bit lists double it (same bytes per tile).
+static int g_norm_tile_elems = 8192;
 
 int set_error(const char* fmt, ...) {
   char buf[1024];
@@ -66,11 +67,11 @@ Tiling elementwise_tiling() {
   Tiling t; t.tile_elems = g_tile_elems; t.ppc = 1; t.chunk_elems = g_tile_elems; return t;
 }
 
-Tiling chunked_tiling(int chunk_size, int tile_scale) {
+Tiling chunked_tiling(int chunk_size, int tile_scale, int fixed_tile_elems) {
   init_tuning();
   Tiling t;
   t.chunk_elems = chunk_size;
-  const int target = g_norm_tile_elems * (tile_scale > 0 ? tile_scale : 1);
+  const int target = (fixed_tile_elems > 0 ? fixed_tile_elems : g_norm_tile_elems) * (tile_scale > 0 ? tile_scale : 1);
   if (chunk_size <= target) { t.tile_elems = chunk_size; t.ppc = 1; return t; }
   int ppc = (chunk_size + target - 1) / target;
   int tile = (chunk_size + ppc - 1) / ppc;

@@ -50,8 +50,9 @@ struct Tiling {
 Tiling elementwise_tiling();
 // Norm ops: a chunk of `chunk_size` elements is split into ppc tiles so that the per-chunk
 // overflow check of the reference (csrc/multi_tensor_l2norm_kernel.cu:103) is preserved.
-// tile_scale multiplies the tile length (2 for lists of 16-bit elements only: same bytes per tile).
-Tiling chunked_tiling(int chunk_size, int tile_scale = 1);
+// tile_scale multiplies the tile length (2 for lists of 16-bit elements only: same bytes per tile);
+// fixed_tile_elems > 0 replaces the tunable default (callers whose scratch is sized for one tile length).
+Tiling chunked_tiling(int chunk_size, int tile_scale = 1, int fixed_tile_elems = 0);
 
 // Validates the list set (depth, counts, null pointers) and returns a device-resident table for
 // it on `stream`, uploading only when no cached copy matches.

@@ -38,7 +38,7 @@ struct MaxNormOp : OpBase {
   using Types = TypeList<Tx>;
   static constexpr unsigned STORES = 0;
   static constexpr int VEC = (Elem<Tx>::SIZE == 2) ? 8 : 4;
-  static constexpr int UNROLL = 4;
+  static constexpr int UNROLL = (Elem<Tx>::SIZE == 2) ? 1 : 4;   // as L2NormOp
   static constexpr int THREADS = 256;
   struct State { float acc = 0.f; };
   float* partials;
@@ -57,7 +57,7 @@ struct SumSqOp : OpBase {
   using Types = TypeList<Tx>;
   static constexpr unsigned STORES = 0;
   static constexpr int VEC = (Elem<Tx>::SIZE == 2) ? 8 : 4;
-  static constexpr int UNROLL = 4;
+  static constexpr int UNROLL = (Elem<Tx>::SIZE == 2) ? 1 : 4;   // as L2NormOp
   static constexpr int THREADS = 256;
   struct State { float acc = 0.f; };
   float* partials;

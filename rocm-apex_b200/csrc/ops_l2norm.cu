@@ -11,12 +11,15 @@ namespace b200mt {
 #ifndef B200MT_NORM16_VEC
 #define B200MT_NORM16_VEC 8   // 16-bit inputs: 8 elements = one 128-bit load per access
 #endif
+#ifndef B200MT_NORM16_UNROLL
+#define B200MT_NORM16_UNROLL 1   // swept 1/2/4/8 on 4x256M fp16: 312 / 325 / 394 / 552 us (profiles/sweep_norm2_r01.txt)
+#endif
 template <typename Tx>
 struct L2NormOp : OpBase {
   using Types = TypeList<Tx>;
   static constexpr unsigned STORES = 0;
   static constexpr int VEC = (Elem<Tx>::SIZE == 2) ? B200MT_NORM16_VEC : 4;
-  static constexpr int UNROLL = 4;
+  static constexpr int UNROLL = (Elem<Tx>::SIZE == 2) ? B200MT_NORM16_UNROLL : 4;
   static constexpr int THREADS = 256;
   struct State { float acc = 0.f; };
   float* partials;

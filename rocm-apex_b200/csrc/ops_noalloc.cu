@@ -14,9 +14,9 @@
 //  * the array is B200MT_NOALLOC_SCRATCH_BYTES (about 257 KiB) of device memory on EVERY GPU that
 //    loads this library, from load until the process exits, whether or not this function is called;
 //  * inputs needing more than B200MT_NOALLOC_MAX_TILES (65536) scheduling tiles are refused with an
-//    error -- with the default norm tile of 16384 elements and chunk_size >= 16384 that is
-//    1,073,741,824 elements; small chunk sizes lower it (one tile per chunk at least), and so does a
-//    smaller B200MT_NORM_TILE_ELEMS;
+//    error -- tiles are 16384 elements here whatever B200MT_NORM_TILE_ELEMS says, so with
+//    chunk_size >= 16384 that is 1,073,741,824 elements; small chunk sizes lower it (one tile per
+//    chunk at least);
 //  * all calls on a device share the array and it keeps whatever the previous call left in it.  The
 //    function re-initialises the few words that must start at zero itself, at the head of its own
 //    work on the stream, so back-to-back calls on one stream are fine; two calls whose GPU work can
@@ -98,7 +98,7 @@ extern "C" int b200mt_l2norm_flat_noalloc(const void* x, int dtype, int64_t nume
   B200MT_CHECK(chunk_size > 0, "chunk_size must be > 0 (got %d)", chunk_size);
   B200MT_CHECK(noop != nullptr && ret != nullptr, "noop / ret pointer is NULL");
   B200MT_CHECK(numel >= 0 && (numel == 0 || x != nullptr), "bad input buffer");
-  const Tiling tiling = chunked_tiling(chunk_size);
+  const Tiling tiling = chunked_tiling(chunk_size, 1, 16384);   // fixed: the array is sized in tiles of this length
   const long long full = numel / tiling.chunk_elems, rem = numel % tiling.chunk_elems;
   const long long ntiles = full * tiling.ppc + (rem + tiling.tile_elems - 1) / tiling.tile_elems;
   B200MT_CHECK(ntiles <= kNoallocMaxTiles,
