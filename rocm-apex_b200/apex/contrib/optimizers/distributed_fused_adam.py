@@ -282,10 +282,21 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                 for p, v in zip(self._model_params, self._param_views):
                     v.copy_(p.detach())
                     p.data = v
+        self._ag_pg = self._pg
         if self._cuda:
             self._comm_stream = torch.cuda.Stream(device=dev)
+            self._ag_stream = self._comm_stream
             self._rs_done = [torch.cuda.Event() for _ in range(K)]
             self._adam_done = [torch.cuda.Event() for _ in range(K)]
+            if (W > 1 and K > 1 and not self._fused
+                    and dist.get_process_group_ranks(self._pg) == list(range(dist.get_world_size()))):
+                # The all-gathers get their own communicator and stream (the reference does the same with its
+                # dwu_num_ag_pg groups, :345-364): AG(k) then runs while RS(k-1..0) are still in flight -- the
+                # reduce-scatter loads a GPU's outgoing links, the all-gather its incoming ones -- instead of queueing
+                # behind them on one communicator.  Only when the optimizer spans the whole job: new_group() is
+                # collective over the default group.
+                self._ag_pg = dist.new_group(ranks=list(range(W)))
+                self._ag_stream = torch.cuda.Stream(device=dev)
         # overlapped reductions (reference :158-164,381-395,489-502): a hook per parameter marks its gradient
         # as produced; pipeline chunks are flushed (flattened + reduce-scattered on the side stream) from the
         # LAST chunk down, each as soon as every parameter that touches it has its gradient -- backward
@@ -466,11 +477,12 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                 cur.wait_event(self._rs_done[k])
                 self._adam_chunk(k, combined_scale)
                 self._adam_done[k].record(cur)
-            with torch.cuda.stream(self._comm_stream):          # AG(k) behind Adam(k), on the comm stream
+            with torch.cuda.stream(self._ag_stream):            # AG(k) behind Adam(k), beside the remaining RS
                 for k in order:
-                    self._comm_stream.wait_event(self._adam_done[k])
+                    self._ag_stream.wait_event(self._adam_done[k])
                     dist.all_gather_into_tensor(self._new_params[k * chunk:(k + 1) * chunk],
-                                                self._fp16_p[k * shard:(k + 1) * shard], group=self._pg)
+                                                self._fp16_p[k * shard:(k + 1) * shard], group=self._ag_pg)
+            cur.wait_stream(self._ag_stream)
             cur.wait_stream(self._comm_stream)
         else:
             for k in range(K):
