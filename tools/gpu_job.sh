@@ -1,3 +1,6 @@
 mkdir -p gpurun_out
-for t in 3072 3584 3840 4000 4096 4352 4608 5120 6144; do B200MT_TILE_ELEMS=$t B200MT_BENCH_SKIP_CPU=1 python bench.py --steps 100 --warmup 5 2>/dev/null | tail -1 | python -c "
-import sys,json; d=json.loads(sys.stdin.readline()); print($t, round(d['ms_per_step']*1e3,2), round(d['roofline']['avg_launch_ms']*1e3,2), round(d['roofline']['frac'],4), round(d['mixed_precision_adam']['ms_per_launch']*1e3,2))"; done
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; tail -3 gpurun_out/pytest_gpu.log
+python tools/bench_configs.py --out gpurun_out/configs_final.md > gpurun_out/configs_final.jsonl 2> gpurun_out/configs_final.err; tail -2 gpurun_out/configs_final.err; wc -l gpurun_out/configs_final.md
+python bench.py > gpurun_out/bench_full.log 2>&1; tail -1 gpurun_out/bench_full.log | cut -c1-200
+python bench.py --impl reference --steps 3 --warmup 1 2>/dev/null | tail -1 | cut -c1-200
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
