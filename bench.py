@@ -334,13 +334,20 @@ def run_single(args):
     for k in range(3):
         e2e_step(k + 1)
     torch.cuda.synchronize()
-    e0.record(stream)
-    for k in range(e2e_steps):
-        ov = e2e_step(k + 4)
-    e1.record(stream)
-    torch.cuda.synchronize()
-    e2e_ms = e0.elapsed_time(e1) / e2e_steps
-    assert ov == 0
+    # The host's PCIe complex is shared with other tenants of the box: the same pinned buffer copies at 55 GB/s one
+    # moment and 35 GB/s the next (tools/e2e_probe.py).  Time E2E_BLOCKS blocks of e2e_steps steps and report the
+    # median block, all blocks listed beside it.
+    E2E_BLOCKS = 5
+    e2e_blocks = []
+    for blk in range(E2E_BLOCKS):
+        e0.record(stream)
+        for k in range(e2e_steps):
+            ov = e2e_step(k + 4)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        e2e_blocks.append(e0.elapsed_time(e1) / e2e_steps)
+        assert ov == 0
+    e2e_ms = statistics.median(e2e_blocks)
 
     # ---- the same device-resident step through the drop-in Python entry points (amp_C.*): what the
     # reference's optimizers call.  Host time per call is measured separately (no sync inside).
@@ -442,6 +449,7 @@ def run_single(args):
         "e2e": {"value": nparams / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 4 * nparams, "d2h_bytes_per_step": 4,
                 "ms_per_step": e2e_ms, "steps": e2e_steps,
                 "segments": len(bounds) - 1, "pcie_floor_ms_at_55GBs": 4 * nparams / 55e9 * 1e3,
+                "blocks_ms_per_step": e2e_blocks, "statistic": "median of %d blocks of %d steps" % (E2E_BLOCKS, e2e_steps),
                 "api": "pinned-host gradients copied in %d segments on a copy stream; per segment amp_C.multi_tensor_scale + "
                        "amp_C.multi_tensor_adam (drop-in entry points); flag.item() at the end" % (len(bounds) - 1)},
         "gpu_launches": int(launches),
