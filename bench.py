@@ -107,12 +107,24 @@ def gpu_numa_cpus(dev_index):
         bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
         node = int(open("/sys/bus/pci/devices/%s/numa_node" % bdf).read())
         if node < 0:
-            return None
+            raise ValueError("no NUMA node recorded for %s" % bdf)
         cpus = set()
         for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
             a, _, b = part.partition("-")
             cpus.update(range(int(a), int(b or a) + 1))
         return (cpus & os.sched_getaffinity(0)) or None
+    except Exception:
+        pass
+    try:    # containers often hide sysfs NUMA data; the driver still knows which CPUs sit next to the GPU
+        import pynvml
+        pynvml.nvmlInit()
+        pr = torch.cuda.get_device_properties(dev_index)
+        bdf = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bdf.encode())
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+        near = cpus & os.sched_getaffinity(0)
+        return near if (near and near != os.sched_getaffinity(0)) else None
     except Exception:
         return None
 
