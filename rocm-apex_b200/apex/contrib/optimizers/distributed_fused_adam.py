@@ -19,8 +19,9 @@ has_overflow / peek_overflow, strided_check_finite(), state_dict() = {step, fp32
     Adam(k), AG(k) overlaps Adam(k+1..);
   * gradients are flattened with ONE multi_tensor_scale launch and gathered parameters are scattered
     back with ONE maybe_cast_mt launch, whatever the number of parameters.
-The kwargs that only steer the reference's process-group fan-out (dwu_num_rs_pg, dwu_num_ar_pg,
-dwu_num_ag_pg, dwu_group_size, num_process_groups, ...) are accepted and ignored.
+`dwu_group_size` keeps its meaning (shard inside groups of that many ranks, all-reduce the shard across groups: the
+multi-node layout).  The kwargs that only steer the reference's process-group fan-out (dwu_num_rs_pg, dwu_num_ar_pg,
+dwu_num_ag_pg, num_process_groups, ...) are accepted and ignored.
 """
 import importlib
 import math
@@ -173,6 +174,27 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         self._pg = current_process_group if current_process_group is not None else dist.group.WORLD
         self._world_size = dist.get_world_size(self._pg)
         self._rank = dist.get_rank(self._pg)
+        # dwu_group_size (reference :115-117,328-345,397-418): shard over groups of that many ranks (one node) and keep
+        # the optimizer state replicated across groups; gradients are reduce-scattered inside a group, then the
+        # shard is all-reduced across groups.  0 or >= the world: one group, the plain ZeRO layout.
+        self._bcast_pg, self._grad_world, self._ar_pg = self._pg, self._world_size, None
+        if 0 < dwu_group_size < self._world_size:
+            if self._world_size % dwu_group_size != 0:
+                raise ValueError("dwu_group_size %d does not divide the %d ranks" % (dwu_group_size, self._world_size))
+            if self._fused:
+                raise NotImplementedError("fused_collectives spans one NVSwitch domain: no rank groups")
+            if current_process_group is not None:
+                raise NotImplementedError("rank groups inside a caller-provided process group")   # new_group() is world-collective
+            gs, ngroups, me = dwu_group_size, self._world_size // dwu_group_size, self._rank
+            for j in range(ngroups):                       # every rank creates every group, in the same order
+                g = dist.new_group(ranks=[j * gs + k for k in range(gs)])
+                if me // gs == j:
+                    self._pg = g
+            for j in range(gs):
+                g = dist.new_group(ranks=[j + k * gs for k in range(ngroups)])
+                if me % gs == j:
+                    self._ar_pg = g
+            self._world_size, self._rank = gs, me % gs
 
     # ------------------------------------------------------------------------------------------
     # lazy construction of the flat buffers (first complete_reductions / step)
@@ -187,12 +209,12 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                     self._model_params.append(p)
                     self._group_of.append(gi)
         assert len(self._model_params) > 0, "no parameters to optimise"
-        if self._world_size > 1:
+        if self._grad_world > 1:
             # every rank starts from the first rank's parameters (reference :144-145)
-            src = dist.get_global_rank(self._pg, 0)
+            src = dist.get_global_rank(self._bcast_pg, 0)
             for group in self.param_groups:
                 for p in group["params"]:
-                    dist.broadcast(p.data, src=src, group=self._pg)
+                    dist.broadcast(p.data, src=src, group=self._bcast_pg)
         p0 = self._model_params[0]
         dev, low = p0.device, p0.dtype
         assert all(p.dtype == low and p.device == dev for p in self._model_params), \
@@ -370,6 +392,8 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         shard, chunk = self._layout["shard"], self._layout["chunk"]
         dist.reduce_scatter_tensor(self._fp16_g[k * shard:(k + 1) * shard],
                                    self._flat_grads[k * chunk:(k + 1) * chunk], group=self._pg)
+        if self._ar_pg is not None:         # the same shard of the other rank groups (reference :411-418)
+            dist.all_reduce(self._fp16_g[k * shard:(k + 1) * shard], group=self._ar_pg)
         if self._cuda:
             self._rs_done[k].record(torch.cuda.current_stream(self._device))
 
@@ -377,7 +401,7 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         """Flatten (predivide + copy, ONE launch) the not yet flattened gradients of every parameter touching
         `chunks`, then reduce-scatter those chunks on the communication stream.  `final`: parameters without a
         gradient are treated as unused (zero), as complete_reductions() does in the reference (:556-564)."""
-        scale = 1.0 / self._world_size if self._predivide else 1.0
+        scale = 1.0 / self._grad_world if self._predivide else 1.0      # every rank of every group contributes
         src, dst, inplace = [], [], []
         for k in chunks:
             for i in self._chunk_params[k]:

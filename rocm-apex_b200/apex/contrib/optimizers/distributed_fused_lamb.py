@@ -34,7 +34,8 @@ class DistributedFusedLAMB(DistributedFusedAdam):
         if not clip_after_ar:
             raise NotImplementedError("clip_after_ar=False (clipping before the reduction) is not part of this path")
         super().__init__(params, lr=lr, bias_correction=bias_correction, betas=betas, eps=eps, weight_decay=weight_decay,
-                         max_grad_norm=max_grad_norm, overlap_reductions=overlap_reductions, dwu_num_blocks=1,
+                         max_grad_norm=max_grad_norm, overlap_reductions=overlap_reductions,
+                         dwu_group_size=dwu_group_size, dwu_num_blocks=1,
                          dwu_num_chunks=1, predivide=True, e5m2_allgather=e5m2_allgather,
                          step_supports_amp_scaling=step_supports_amp_scaling, zero_copy_params=zero_copy_params)
         for g in self.param_groups:

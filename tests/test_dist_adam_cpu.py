@@ -260,6 +260,75 @@ def _worker_overlap(rank, world, port, K, dtype_name, out):
         dist.destroy_process_group()
 
 
+def _worker_groups(rank, world, port, K, gs, out):
+    """dwu_group_size < world (reference :115-117,328-345,411-418): shards inside groups of `gs` ranks, state
+    replicated across groups, gradients reduce-scattered in the group and all-reduced across groups."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    for p in (os.path.join(ROOT, "rocm-apex_b200"), ROOT):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import apex  # noqa: F401
+        _install_kernel_doubles()
+        from apex.contrib.optimizers.distributed_fused_adam import DistributedFusedAdam
+        shapes = [(300, 7), (64,), (5,), (1000, 3), (1,)]
+        g0 = torch.Generator().manual_seed(7)
+        init = [torch.randn(s, generator=g0) * 0.1 for s in shapes]
+        params = [torch.nn.Parameter(t.clone()) for t in init]
+        opt = DistributedFusedAdam(params, lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=0.01, dwu_group_size=gs,
+                                   dwu_num_blocks=K, dwu_num_chunks=1, compute_L2_grad_norm=True, overlap_reductions=False)
+        opt.set_global_scale(8.0)
+        assert opt._world_size == gs and opt._rank == rank % gs and opt._grad_world == world
+        masters = [t.clone().requires_grad_() for t in init]
+        ref = torch.optim.AdamW(masters, lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=0.01)
+        for it in range(3):
+            per_rank = []
+            for r in range(world):
+                gr = torch.Generator().manual_seed(100 * it + r)
+                per_rank.append([torch.randn(s, generator=gr) * 8.0 for s in shapes])
+            for p, g in zip(params, per_rank[rank]):
+                p.grad = g.clone()
+            opt.complete_reductions()
+            avg = [sum(gs_[i] / world for gs_ in per_rank) for i in range(len(shapes))]
+            want_norm = torch.sqrt(sum((a * a).sum() for a in avg))
+            assert abs(opt.L2_grad_norm - float(want_norm)) <= 1e-4 * float(want_norm)
+            opt.step()
+            for m, a in zip(masters, avg):
+                m.grad = a / 8.0
+            ref.step()
+            for p, m in zip(params, masters):
+                assert torch.allclose(p.detach(), m.detach(), rtol=1e-5, atol=1e-6), (it, rank)
+        # state is sharded inside a group and replicated across groups
+        assert opt._fp32_p.numel() == opt._layout["shard"] * K and opt._layout["world_size"] == gs
+        gathered = [torch.zeros_like(opt._fp32_m) for _ in range(world)]
+        dist.all_gather(gathered, opt._fp32_m)
+        for r in range(world):
+            assert torch.equal(gathered[r], gathered[r % gs])
+        assert not torch.equal(gathered[0], gathered[1])
+        with pytest.raises(ValueError):
+            DistributedFusedAdam(params, dwu_group_size=3)
+        out.put((rank, "ok"))
+    except Exception:
+        import traceback
+        out.put((rank, "FAIL: " + traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_rank_groups_world4_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_groups, args=(r, 4, 29680, 2, 2, q)) for r in range(4)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in results:
+        assert msg == "ok", "rank %d: %s" % (rank, msg)
+
+
 @pytest.mark.parametrize("K,dtype_name", [(3, "float32"), (4, "bfloat16")])
 def test_overlapped_reductions_world2_gloo(K, dtype_name):
     ctx = mp.get_context("spawn")

@@ -70,7 +70,7 @@ def _ref_lamb_step(masters, m, v, grads, step, lr, b1, b2, eps, wd, max_norm, nv
         p -= ratio * u
 
 
-def _worker(rank, world, port, backend, out):
+def _worker(rank, world, port, backend, out, group_size=0):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     _paths()
     cuda = backend == "nccl"
@@ -90,8 +90,10 @@ def _worker(rank, world, port, backend, out):
         params = [torch.nn.Parameter(t.clone().to(dev)) for t in init]       # fp32 model params: exact comparison
         lr, b1, b2, eps, wd, max_norm = 1e-2, 0.9, 0.99, 1e-6, 0.01, 1.0
         opt = DistributedFusedLAMB(params, lr=lr, betas=(b1, b2), eps=eps, weight_decay=wd, max_grad_norm=max_norm,
-                                   use_nvlamb=False, overlap_reductions=False)
+                                   use_nvlamb=False, overlap_reductions=False, dwu_group_size=group_size)
         opt.set_global_scale(4.0)
+        if group_size:
+            assert opt._world_size == group_size and opt._grad_world == world
         masters = [t.double() for t in init]
         m = [torch.zeros_like(t) for t in masters]
         v = [torch.zeros_like(t) for t in masters]
@@ -190,10 +192,10 @@ def _worker_e5m2(rank, world, port, backend, out):
         dist.destroy_process_group()
 
 
-def _run(backend, port, worker=None):
+def _run(backend, port, worker=None, world=2, extra=()):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=worker or _worker, args=(r, 2, port, backend, q)) for r in range(2)]
+    procs = [ctx.Process(target=worker or _worker, args=(r, world, port, backend, q) + tuple(extra)) for r in range(world)]
     for p in procs:
         p.start()
     results = [q.get(timeout=300) for _ in procs]
@@ -209,6 +211,12 @@ def test_sharded_lamb_host_logic_world2_gloo():
 
 def test_sharded_lamb_e5m2_allgather_world2_gloo():
     _run("gloo", 29752, _worker_e5m2)
+
+
+def test_sharded_lamb_rank_groups_world4_gloo():
+    """dwu_group_size=2 on 4 ranks: shards inside a group, gradients all-reduced across groups
+    (reference distributed_fused_lamb.py:127-130,148-168)."""
+    _run("gloo", 29754, world=4, extra=(2,))
 
 
 @pytest.mark.gpu
