@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _worker(rank, world, port, K, zero_copy, fused, out, e5m2=False):
+def _worker(rank, world, port, K, zero_copy, fused, out, e5m2=False, group_size=0):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     for p in (os.path.join(ROOT, "rocm-apex_b200"), ROOT):
         if p not in sys.path:
@@ -30,7 +30,8 @@ def _worker(rank, world, port, K, zero_copy, fused, out, e5m2=False):
         params = [torch.nn.Parameter(t.to(dev).bfloat16()) for t in init]
         opt = DistributedFusedAdam(params, lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=0.01, dwu_num_blocks=K,
                                    dwu_num_chunks=1, compute_L2_grad_norm=not fused, overlap_reductions=False,
-                                   zero_copy_params=zero_copy, fused_collectives=fused, e5m2_allgather=e5m2)
+                                   zero_copy_params=zero_copy, fused_collectives=fused, e5m2_allgather=e5m2,
+                                   dwu_group_size=group_size)
         opt.set_global_scale(8.0)
         import fused_adam_cuda
         # unsharded check: our own mixed-precision multi_tensor_adam [g, p32, m32, v32, p_copy] on the averaged grads
@@ -86,7 +87,7 @@ def _worker(rank, world, port, K, zero_copy, fused, out, e5m2=False):
         dist.all_gather(gathered, opt._fp32_p)
         for r in range(world):
             for k in range(K):
-                lo = k * L["chunk"] + r * L["shard"]
+                lo = k * L["chunk"] + (r % L["world_size"]) * L["shard"]     # rank groups replicate the shards
                 full[lo:lo + L["shard"]] = gathered[r][k * L["shard"]:(k + 1) * L["shard"]]
         for off, t in zip(L["offsets"], m32):
             got = full[off:off + t.numel()].view_as(t)
@@ -106,6 +107,22 @@ def test_sharded_adam_matches_unsharded_world2_nccl(K, zero_copy, fused):
     q = ctx.Queue()
     port = 29700 + K + (20 if fused else 0) + (40 if zero_copy else 0)
     procs = [ctx.Process(target=_worker, args=(r, 2, port, K, zero_copy, fused, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in results:
+        assert msg == "ok", "rank %d: %s" % (rank, msg)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_rank_groups_of_one_world2_nccl():
+    """dwu_group_size=1 on 2 ranks: every rank is its own shard group, the gradient 'shard' (everything) is all-reduced
+    across the two groups on the communication stream -- the cross-group leg of the multi-node layout over NCCL."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, 29790, 2, False, False, q, False, 1)) for r in range(2)]
     for p in procs:
         p.start()
     results = [q.get(timeout=300) for _ in procs]
