@@ -53,6 +53,37 @@ def test_reshard_is_a_reslicing_of_the_flat_space():
         reshard_state_dicts(sds, numels, 1, 1, old_num_chunks=3)
 
 
+def test_reshard_tool_command_line(tmp_path):
+    import json
+    import subprocess
+    from apex.contrib.optimizers.distributed_fused_adam import build_layout
+    numels = [2100, 64, 5, 3000, 1, 129]
+    old, new = build_layout(numels, 2, 2), build_layout(numels, 4, 1)
+    g = torch.Generator().manual_seed(9)
+    end = old["offsets"][-1] + numels[-1]
+    fulls = {}
+    for key in ("fp32_p", "fp32_m", "fp32_v"):
+        f = torch.zeros(max(old["total"], new["total"]))
+        f[:end] = torch.randn(end, generator=g)
+        fulls[key] = f
+    files = []
+    for r in range(2):
+        sd = dict(step=5, layout={"world_size": 2, "num_chunks": 2},
+                  **{k: _shard(f[:old["total"]], old, r) for k, f in fulls.items()})
+        files.append(str(tmp_path / ("old%d.pt" % r)))
+        torch.save(sd, files[-1])
+    (tmp_path / "numels.json").write_text(json.dumps(numels))
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "reshard_checkpoint.py"), "--numels", str(tmp_path / "numels.json"),
+                          "--new-world", "4", "--new-chunks", "1", "--out", str(tmp_path / "new{rank}.pt")] + files,
+                         capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    for r in range(4):
+        sd = torch.load(str(tmp_path / ("new%d.pt" % r)))
+        assert sd["step"] == 5 and sd["layout"] == {"world_size": 4, "num_chunks": 1}
+        for k, f in fulls.items():
+            assert torch.equal(sd[k], _shard(f[:new["total"]], new, r))
+
+
 def _grads(it, rank):
     gr = torch.Generator().manual_seed(100 * it + rank)
     return [torch.randn(s, generator=gr) * 4.0 for s in SHAPES]
