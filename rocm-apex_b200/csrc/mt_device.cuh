@@ -646,6 +646,29 @@ __device__ __forceinline__ float div_const(float x, float c, float rc) {
 #endif
 }
 
+// amp_C.multi_tensor_adam's per-element rule (csrc/multi_tensor_adam.cu:94-112), shared by the streaming AdamOp
+// and the bulk-copy kernel of ops_adam_tma.cu so that both give the same bits.
+__device__ __forceinline__ void adam_rule(float gin, float& p, float& m, float& v, float beta1, float beta2,
+                                          float bc1, float bc2, float eps, float lr, float decay, float grad_scale,
+                                          int mode) {
+  float g = gin * grad_scale;
+  const float rbc1 = 1.f / bc1, rbc2 = 1.f / bc2;   // loop-invariant: hoisted by the compiler
+  if (mode == 0) {  // L2: decay folded into the gradient
+    g = g + decay * p;
+    m = beta1 * m + (1.f - beta1) * g;
+    v = beta2 * v + (1.f - beta2) * g * g;
+    const float mu = div_const(m, bc1, rbc1), vu = div_const(v, bc2, rbc2);
+    const float denom = fast_sqrt(vu) + eps;
+    p = p - lr * fast_div(mu, denom);
+  } else {          // AdamW: decoupled decay
+    m = beta1 * m + (1.f - beta1) * g;
+    v = beta2 * v + (1.f - beta2) * g * g;
+    const float mu = div_const(m, bc1, rbc1), vu = div_const(v, bc2, rbc2);
+    const float denom = fast_sqrt(vu) + eps;
+    p = p - lr * (fast_div(mu, denom) + decay * p);
+  }
+}
+
 // Default no-op hooks an Op can inherit.
 struct OpBase {
   struct State {};

@@ -26,6 +26,12 @@
 
 namespace b200mt {
 
+// ops_adam_tma.cu: bulk-copy (TMA) staging for the all-fp32, 16-byte-aligned case
+bool adam_tma_wanted(const b200mt_lists* L);
+int adam_tma_tile();
+int adam_tma_launch(const TableView& tv, float beta1, float beta2, float bc1, float bc2, float eps, float lr,
+                    float decay, float grad_scale, int mode, cudaStream_t stream);
+
 template <typename T> struct is_mc { static constexpr bool value = false; };
 template <> struct is_mc<mc_bf16> { static constexpr bool value = true; };
 template <> struct is_mc<mc_f16> { static constexpr bool value = true; };
@@ -46,22 +52,8 @@ struct AdamOp : OpBase {
   int mode;
   __device__ __forceinline__ unsigned load_mask() const { return 0b01111; }
   __device__ __forceinline__ void elem(State&, float (&x)[NL]) const {
-    float g = x[0] * grad_scale, p = x[1], m = x[2], v = x[3];
-    const float rbc1 = 1.f / bc1, rbc2 = 1.f / bc2;   // loop-invariant: hoisted by the compiler
-    if (mode == 0) {  // L2: decay folded into the gradient
-      g = g + decay * p;
-      m = beta1 * m + (1.f - beta1) * g;
-      v = beta2 * v + (1.f - beta2) * g * g;
-      const float mu = div_const(m, bc1, rbc1), vu = div_const(v, bc2, rbc2);
-      const float denom = fast_sqrt(vu) + eps;
-      p = p - lr * fast_div(mu, denom);
-    } else {          // AdamW: decoupled decay
-      m = beta1 * m + (1.f - beta1) * g;
-      v = beta2 * v + (1.f - beta2) * g * g;
-      const float mu = div_const(m, bc1, rbc1), vu = div_const(v, bc2, rbc2);
-      const float denom = fast_sqrt(vu) + eps;
-      p = p - lr * (fast_div(mu, denom) + decay * p);
-    }
+    float p = x[1], m = x[2], v = x[3];
+    adam_rule(x[0], p, m, v, beta1, beta2, bc1, bc2, eps, lr, decay, grad_scale, mode);
     x[1] = p; x[2] = m; x[3] = v;
     if constexpr (COPY) x[4] = p;
   }
@@ -154,7 +146,11 @@ extern "C" int b200mt_adam(const b200mt_lists* L, int chunk_size, int32_t* noop,
   if (guard.status) return 1;
   cudaStream_t stream = (cudaStream_t)stream_;
   TableView tv;
-  if (acquire_table(L, 4, 5, elementwise_tiling(), stream, &tv)) return 1;
+  B200MT_CHECK(L->depth == 4 || L->depth == 5, "tensor_lists.size() != depth");
+  const bool tma = adam_tma_wanted(L);     // all fp32 and 16-byte aligned: bulk-copy staging with its own tile length
+  Tiling tiling = elementwise_tiling();
+  if (tma) { tiling.tile_elems = adam_tma_tile(); tiling.chunk_elems = tiling.tile_elems; tiling.ppc = 1; }
+  if (acquire_table(L, 4, 5, tiling, stream, &tv)) return 1;
 
   // host-side bias correction, evaluated in double and narrowed (csrc/multi_tensor_adam.cu:145-149)
   float bc1 = 1.f, bc2 = 1.f;
@@ -170,6 +166,7 @@ extern "C" int b200mt_adam(const b200mt_lists* L, int chunk_size, int32_t* noop,
   B200MT_CHECK(L->dtype[2] == dp && L->dtype[3] == dp, "adam: p, m and v must share one dtype");
   if (L->depth == 4) {
     if (dg == dp) {  // the reference's case: one dtype for all four lists
+      if (tma) return adam_tma_launch(tv, beta1, beta2, bc1, bc2, eps, lr, weight_decay, grad_scale, mode, stream);
       return dispatch_f64_f32_f16_bf16(dg, "adam", [&](auto t) {
         using T = typename decltype(t)::type;
         AdamOp<T, T, T, false> op; fill(op);
