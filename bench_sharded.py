@@ -19,7 +19,8 @@ import param_shapes
 NVLINK_GBS = 770.0     # measured peer-copy bandwidth per direction (B200_PROFILING.md); 900 nominal
 
 
-def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, stream, flat, nparams, shapes, model_name, lib):
+def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, stream, flat, nparams, shapes, model_name, lib,
+                  parity=None, parity_ok=True):
     from bench import peaks, pinned_near_gpu, gpu_numa_cpus, METRIC, UNIT
     clocks = sampler.stop() if rank == 0 else None
     host = pinned_near_gpu(1 << 27, torch.bfloat16, local)
@@ -81,9 +82,12 @@ def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, str
                     "api": "DistributedFusedAdam(fused_collectives=True).complete_reductions() + step(), grads copied from pinned host each step"},
             "gpu_launches": int(tl.item()),
             "clocks": clocks,
+            "parity": parity,
         }
         print(json.dumps(line))
     dist.destroy_process_group()
+    if not parity_ok:
+        raise SystemExit("bench_sharded: multi-GPU parity bound violated (see the `parity` block of the JSON line)")
 
 
 def run_sharded(args):
@@ -106,42 +110,79 @@ def run_sharded(args):
     shapes = param_shapes.MODELS[model_name]()
     nparams = param_shapes.numel(shapes)
 
-    # model parameters (bf16).  They are created as views of one flat allocation only to keep set-up fast;
-    # the optimizer re-points them into its all-gather buffer (zero_copy_params) anyway.
-    gen = torch.Generator(device=dev).manual_seed(1)
-    params = []
-    for s in shapes:
-        params.append(torch.nn.Parameter((torch.randn(s, generator=gen, device=dev, dtype=torch.float32) * 0.02).to(torch.bfloat16)))
     # B200MT_SHARDED_E5M2=1 (not the headline): the reference's e5m2_allgather=True -- parameters travel as one byte
     # each and are unpacked into the bf16 model parameters by one extra maybe_cast_mt launch (no zero-copy then)
     e5m2 = os.environ.get("B200MT_SHARDED_E5M2", "0") == "1"
 
     def make(fused_flag, chunks):
+        """Model parameters (bf16, seed 1 on every rank), the optimizer, and its flat gradient buffer filled with
+        randn(seed = 100 + rank): the same state whichever step implementation is built on it."""
+        gen = torch.Generator(device=dev).manual_seed(1)
+        params = []
+        for s in shapes:
+            params.append(torch.nn.Parameter((torch.randn(s, generator=gen, device=dev, dtype=torch.float32) * 0.02).to(torch.bfloat16)))
         o = DistributedFusedAdam(params, lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1, dwu_num_blocks=chunks,
                                  dwu_num_chunks=1, predivide=False, overlap_reductions=False, zero_copy_params=not e5m2,
                                  fused_collectives=fused_flag, e5m2_allgather=e5m2)
         o.set_global_scale(float(world))        # gradients are summed by the reduce-scatter; the kernel divides by W
-        return o, o.attach_flat_grads()
+        fl = o.attach_flat_grads()
+        ggen = torch.Generator(device=dev).manual_seed(100 + rank)
+        piece = 1 << 26
+        for off in range(0, fl.numel(), piece):   # randn(seed = rank) in pieces (fp32 staging)
+            n = min(piece, fl.numel() - off)
+            fl[off:off + n].copy_(torch.randn(n, generator=ggen, device=dev))
+        torch.cuda.synchronize()
+        return o, fl
 
-    try:
-        opt, flat = make(fused, K)
-        ok = torch.ones(1, device=dev)
-    except Exception as e:                      # no multicast-capable symmetric memory on this box
+    def make_fused_or_none():
+        try:
+            o, fl = make(True, 1)
+            ok = torch.ones(1, device=dev)
+        except Exception as e:                      # no multicast-capable symmetric memory on this box
+            sys.stderr.write("bench_sharded: fused multimem path unavailable (%r)\n" % (e,))
+            ok, o, fl = torch.zeros(1, device=dev), None, None
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)   # every rank switches together
+        return (o, fl) if float(ok) != 0.0 else (None, None)
+
+    # ---- parity before anything is timed (tools/multi_gpu_parity.py): one step of BOTH step implementations from
+    # identical state, each compared with the unsharded single-GPU kernel on a sample of every rank's shard and on the
+    # gathered parameters of every rank; then the sharded LAMB and the DDP bucket path on small models.  A violated bound
+    # makes the run exit non-zero after the JSON line is printed.
+    parity, parity_ok = None, True
+    if os.environ.get("B200MT_SHARDED_PARITY", "1") == "1":
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import multi_gpu_parity as mgp
+        parity = {"reference_test": "tests/L0/run_optimizers/test_dist_adam.py:119-173 (N-rank DistributedFusedAdam vs the unsharded optimizer)",
+                  "unsharded_kernel": "b200mt_dist_adam on the same reduced gradient (pinned to the reference's kernel by tests/test_parity_gpu.py)"}
+        o1, _ = make(False, K if not fused else int(os.environ.get("B200MT_SHARDED_CHUNKS", "8")))
+        parity["nccl_vs_unsharded"], ok1 = mgp.sharded_adam_parity(o1)
+        del o1, _
+        import gc
+        gc.collect(); torch.cuda.empty_cache()
+        ok2 = True
+        if fused:
+            opt, flat = make_fused_or_none()
+            if opt is not None:
+                parity["fused_vs_unsharded"], ok2 = mgp.sharded_adam_parity(opt)
+            else:
+                fused = False
+                parity["fused_vs_unsharded"] = "multicast memory unavailable"
+        parity["sharded_lamb_vs_unsharded_f64"], ok3 = mgp.sharded_lamb_parity(dev, rank, world)
+        parity["ddp_bucket_path_vs_mean_gradient"], ok4 = mgp.ddp_parity(dev, rank, world)
+        parity_ok = bool(ok1 and ok2 and ok3 and ok4)
+        parity["ok"] = parity_ok
         if not fused:
-            raise
-        sys.stderr.write("bench_sharded: fused multimem path unavailable (%r); timing the NCCL pipeline\n" % (e,))
-        ok = torch.zeros(1, device=dev)
-        opt = flat = None
-    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-    if fused and float(ok) == 0.0:              # every rank switches together
-        fused = False
-        K = int(os.environ.get("B200MT_SHARDED_CHUNKS", "8"))
-        opt, flat = make(False, K)
-    ggen = torch.Generator(device=dev).manual_seed(100 + rank)
-    piece = 1 << 26
-    for off in range(0, flat.numel(), piece):   # randn(seed = rank) in pieces (fp32 staging)
-        n = min(piece, flat.numel() - off)
-        flat[off:off + n].copy_(torch.randn(n, generator=ggen, device=dev))
+            K = int(os.environ.get("B200MT_SHARDED_CHUNKS", "8"))
+            opt, flat = make(False, K)
+    else:
+        opt = None
+        if fused:
+            opt, flat = make_fused_or_none()
+            if opt is None:
+                fused = False
+        if opt is None:
+            K = int(os.environ.get("B200MT_SHARDED_CHUNKS", "8"))
+            opt, flat = make(False, K)
     torch.cuda.synchronize()
     lib = mt.lib
 
@@ -174,7 +215,8 @@ def run_sharded(args):
 
     shard_elems = opt._layout["shard"] * K
     if fused:
-        return _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, stream, flat, nparams, shapes, model_name, lib)
+        return _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, stream, flat, nparams, shapes, model_name, lib,
+                             parity, parity_ok)
     # shard kernel alone (no collectives): the roofline of the dominant kernel on this rank
     ks = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     kreps = 5
@@ -263,6 +305,9 @@ def run_sharded(args):
                     "api": "DistributedFusedAdam.complete_reductions() + step(), grads copied from pinned host each step"},
             "gpu_launches": int(tl.item()),
             "clocks": clocks,
+            "parity": parity,
         }
         print(json.dumps(line))
     dist.destroy_process_group()
+    if not parity_ok:
+        raise SystemExit("bench_sharded: multi-GPU parity bound violated (see the `parity` block of the JSON line)")

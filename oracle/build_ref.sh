@@ -7,9 +7,12 @@
 #   amp_C_ref.so               <- csrc/multi_tensor_*.cu + csrc/amp_C_frontend.cpp
 #   distributed_adam_cuda_ref.so <- apex/contrib/csrc/optimizers/multi_tensor_distopt_adam*.{cpp,cu}
 #   fused_adam_cuda_ref.so     <- apex/contrib/csrc/optimizers/fused_adam_cuda*.{cpp,cu}
+#   distributed_lamb_cuda_ref.so <- apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb*.{cpp,cu}
 # The reference's setup.py cannot be used (it shells out to /opt/rocm/bin/rocminfo at import,
 # setup.py:15-17), so this is a direct nvcc/g++ recipe with the flags setup.py:210 uses
-# (-O3 --use_fast_math -lineinfo + the VERSION_GE_* macros, setup.py:145-154).
+# (-O3 --use_fast_math -lineinfo + the VERSION_GE_* macros, setup.py:145-154) plus the four
+# -D__CUDA_NO_HALF*/BFLOAT16* defines torch's CUDAExtension adds to every nvcc line (without them
+# multi_tensor_distopt_lamb_kernel.cu:352 meets an ambiguous operator!= on at::Half).
 # Only tests/, __graft_entry__.smoke() and bench.py's comparison legs may load these.
 set -euo pipefail
 REF=${REF:-/root/reference}
@@ -25,7 +28,8 @@ TORCH=$($PY -c 'import torch,os;print(os.path.dirname(torch.__file__))')
 PYINC=$($PY -c 'import sysconfig;print(sysconfig.get_paths()["include"])')
 INC="-I$REF/csrc -I$TORCH/include -I$TORCH/include/torch/csrc/api/include -I$PYINC -I/usr/local/cuda/include"
 DEFS="-DVERSION_GE_1_1 -DVERSION_GE_1_3 -DVERSION_GE_1_5 -DTORCH_API_INCLUDE_EXTENSION_H"
-NVFLAGS="-O3 -std=c++17 --use_fast_math -lineinfo --expt-relaxed-constexpr -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC -w"
+NOHALF="-D__CUDA_NO_HALF_OPERATORS__ -D__CUDA_NO_HALF_CONVERSIONS__ -D__CUDA_NO_BFLOAT16_CONVERSIONS__ -D__CUDA_NO_HALF2_OPERATORS__"
+NVFLAGS="$NOHALF -O3 -std=c++17 --use_fast_math -lineinfo --expt-relaxed-constexpr -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC -w"
 LIBS="-L$TORCH/lib -ltorch -ltorch_cpu -ltorch_cuda -lc10 -lc10_cuda -ltorch_python -L/usr/local/cuda/lib64 -lcudart -Wl,-rpath,$TORCH/lib"
 JOBS=${JOBS:-8}
 
@@ -66,4 +70,7 @@ build_module distributed_adam_cuda_ref \
 build_module fused_adam_cuda_ref \
   $REF/apex/contrib/csrc/optimizers/fused_adam_cuda.cpp \
   $REF/apex/contrib/csrc/optimizers/fused_adam_cuda_kernel.cu
+build_module distributed_lamb_cuda_ref \
+  $REF/apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb.cpp \
+  $REF/apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb_kernel.cu
 rm -rf "$OBJ"

@@ -170,6 +170,7 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         self._resume_state = None
         self._reduced = False
         self._last_step = False
+        self._iter_started = False       # the overflow flag has been cleared for the current iteration
 
         self._pg = current_process_group if current_process_group is not None else dist.group.WORLD
         self._world_size = dist.get_world_size(self._pg)
@@ -402,6 +403,12 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         `chunks`, then reduce-scatter those chunks on the communication stream.  `final`: parameters without a
         gradient are treated as unused (zero), as complete_reductions() does in the reference (:556-564)."""
         scale = 1.0 / self._grad_world if self._predivide else 1.0      # every rank of every group contributes
+        if not self._iter_started:
+            # first flush of this iteration: the flag of the flatten pass starts from zero, as the reference's
+            # _flatten_grad_mt does (:481) -- otherwise one non-finite gradient would gate maybe_cast_mt in step()
+            # for the rest of the run and the model parameters would silently stop following the masters
+            self._overflow_buf.zero_()
+            self._iter_started = True
         src, dst, inplace = [], [], []
         for k in chunks:
             for i in self._chunk_params[k]:
@@ -448,6 +455,7 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         with torch.no_grad():
             self._flush_chunks(list(range(self._next_chunk, -1, -1)), final=True)
         self._next_chunk = self._num_chunks_total - 1
+        self._iter_started = False
         self._grad_ready = [False] * len(self._grad_ready)
         self._grad_flat = [False] * len(self._grad_flat)
         self._L2_grad_norm, self._l2_sq = None, None

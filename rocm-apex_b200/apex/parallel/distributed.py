@@ -108,7 +108,9 @@ class DistributedDataParallel(Module):
     overlapped with the rest of backward (reference :129-640).  Iteration 1 records the order in which
     gradients arrive (rank 0's order is broadcast so every rank builds the same buckets) and reduces
     everything at the end of backward; from iteration 2 on a bucket is reduced as soon as its last gradient
-    has been produced."""
+    has been produced AND every earlier bucket has been launched: all ranks issue their all_reduce calls in
+    bucket-index order whatever order their own gradients arrive in (reference comm_ready_buckets, :520-554).
+    With allreduce_trigger_params the buckets are cut at those parameters in iteration 1 (reference :373-376)."""
 
     def __init__(self, module, message_size=10000000, delay_allreduce=False, shared_param=None,
                  allreduce_trigger_params=None, retain_allreduce_buffers=False, allreduce_always_fp32=False,
@@ -147,6 +149,9 @@ class DistributedDataParallel(Module):
         self._index = {id(p): i for i, p in enumerate(self._params)}
         self._multi_tensor_scale = _scale_op()
         self._buckets = None            # fixed after the first iteration
+        self._next_bucket = 0           # index of the next bucket that may be launched (in-order rule)
+        self._ready = set()             # filled buckets waiting for an earlier one
+        self._num_regular = 0           # buckets of parameters whose gradients showed up in iteration 1
         self._bucket_of = {}
         self._arrival = []
         self._callback_queued = False
@@ -188,34 +193,53 @@ class DistributedDataParallel(Module):
                 return
             b = self._bucket_of[id(param)]
             b.pending -= 1
-            ready = (b.pending == 0) if self.trigger_ids is None else (id(param) in self.trigger_ids)
-            if ready and not b.launched:
-                self._reduce_bucket(b)
+            if b.pending == 0 and not b.launched and not b.straggler:
+                # launch strictly in bucket order: a bucket that fills early waits for its predecessors
+                self._ready.add(b.index)
+                while self._next_bucket in self._ready:
+                    self._ready.discard(self._next_bucket)
+                    self._reduce_bucket(self._buckets[self._next_bucket])
+                    self._next_bucket += 1
         return hook
 
     def _build_buckets(self):
         """Buckets in rank 0's gradient-arrival order, one dtype each, closed once they reach message_size
         elements (reference :340-404); parameters whose gradient did not show up in iteration 1 go last."""
         order = list(dict.fromkeys(self._arrival))
+        narrived = len(order)
         order += [i for i in range(len(self._params)) if i not in set(order)]
-        t = torch.tensor(order, dtype=torch.int64, device=self._params[0].device)
+        t = torch.tensor([narrived] + order, dtype=torch.int64, device=self._params[0].device)
         dist.broadcast(t, 0)
-        order = t.tolist()
-        open_by_type, buckets = {}, []
-        for i in order:
-            p = self._params[i]
-            key = (p.dtype, p.device)
-            cur = open_by_type.setdefault(key, [])
-            cur.append(p)
-            if not self.delay_allreduce and sum(q.numel() for q in cur) >= self.message_size:
-                buckets.append(cur)
-                open_by_type[key] = []
-        buckets += [cur for cur in open_by_type.values() if cur]
+        narrived, order = int(t[0]), t[1:].tolist()
+        trigger_idx = None
+        if self.trigger_ids is not None:
+            trigger_idx = set(i for i, p in enumerate(self._params) if id(p) in self.trigger_ids)
+
+        def cut(indices):
+            open_by_type, out = {}, []
+            for i in indices:
+                p = self._params[i]
+                key = (p.dtype, p.device)
+                cur = open_by_type.setdefault(key, [])
+                cur.append(p)
+                if self.delay_allreduce:
+                    continue
+                full = (i in trigger_idx) if trigger_idx is not None else (sum(q.numel() for q in cur) >= self.message_size)
+                if full:
+                    out.append(cur)
+                    open_by_type[key] = []
+            return out + [cur for cur in open_by_type.values() if cur]
+
+        regular = cut(order[:narrived])
+        # parameters whose gradient never showed up on rank 0 in iteration 1 (unused parameters) live in buckets of
+        # their own at the end: those cannot fill during backward and are reduced, in order, by the epilogue
+        stragglers = cut(order[narrived:])
+        self._num_regular = len(regular)
         self._buckets = []
-        for k, params in enumerate(buckets):
+        for k, params in enumerate(regular + stragglers):
             comm_dtype = torch.float32 if self.allreduce_always_fp32 else params[0].dtype
             b = _Bucket(params, comm_dtype)
-            b.index, b.launched = k, False
+            b.index, b.launched, b.straggler = k, False, k >= len(regular)
             self._buckets.append(b)
             for p in params:
                 self._bucket_of[id(p)] = b
@@ -256,9 +280,19 @@ class DistributedDataParallel(Module):
         self._callback_queued = False
         if self._disable_allreduce:
             return
-        if self._buckets is None:
+        first = self._buckets is None
+        if first:
             self._build_buckets()
-        for b in self._buckets:
+        if not first and not self.delay_allreduce and self._next_bucket != self._num_regular:
+            # an overlapped bucket never filled on this rank: the other ranks have (or will) run its all_reduce, so
+            # going on would hang or mix buckets -- same refusal as the reference's epilogue (:339-349)
+            nb, self._next_bucket = self._next_bucket, 0
+            self._ready.clear()
+            for b in self._buckets:
+                b.launched, b.pending = False, len(b.params)
+            raise RuntimeError("In epilogue, next_bucket ({}) != num_buckets ({}).  This probably indicates some buckets "
+                               "were not allreduced.".format(nb, self._num_regular))
+        for b in self._buckets:       # iteration 1 / delayed mode: everything; otherwise the straggler buckets, in order
             if not b.launched:
                 self._reduce_bucket(b, on_main_stream=self.delay_allreduce)
         if self._cuda:
@@ -268,6 +302,8 @@ class DistributedDataParallel(Module):
         for b in self._buckets:
             b.launched = False
             b.pending = len(b.params)
+        self._next_bucket = 0
+        self._ready.clear()
 
 
 class _NullContext(object):

@@ -137,7 +137,7 @@ def _worker(rank, world, port, backend, out):
             g = half.a.weight.grad.float()
             gs = [torch.zeros_like(g) for _ in range(world)]
             dist.all_gather(gs, g)
-            assert torch.equal(gs[0], gs[1]) and ddp._buckets[0].flat.dtype == torch.float32
+            assert all(torch.equal(gs[0], x) for x in gs) and ddp._buckets[0].flat.dtype == torch.float32
         # Reducer: manual all-reduce of a module's gradients
         model = copy.deepcopy(base)
         red = Reducer(model)
@@ -155,10 +155,10 @@ def _worker(rank, world, port, backend, out):
         dist.destroy_process_group()
 
 
-def _run(backend, port):
+def _run(backend, port, world=2):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, backend, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, backend, q)) for r in range(world)]
     for p in procs:
         p.start()
     results = [q.get(timeout=300) for _ in procs]
@@ -176,3 +176,106 @@ def test_ddp_world2_gloo():
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 def test_ddp_world2_nccl():
     _run("nccl", 29771)
+
+
+@pytest.mark.gpu
+def test_ddp_world1_nccl_one_gpu():
+    """1-rank NCCL job on one GPU: bucket building, the flat-bucket multi_tensor_scale gather / scatter launches on the
+    side streams and the all_reduce call run for real; the expected gradient is the local one."""
+    _run("nccl", 29772, world=1)
+
+
+class TwoBranch(torch.nn.Module):
+    """Two independent same-shaped layers: the order in which they are evaluated decides the order in which autograd
+    produces their gradients (later nodes first)."""
+
+    def __init__(self):
+        super().__init__()
+        self.a = torch.nn.Linear(32, 32)
+        self.b = torch.nn.Linear(32, 32)
+
+    def forward(self, x, a_last=False, skip_b=False):
+        if skip_b:
+            return self.a(x).pow(2).mean()
+        if a_last:
+            yb = self.b(x); ya = self.a(x)
+        else:
+            ya = self.a(x); yb = self.b(x)
+        return ya.pow(2).mean() + 2.0 * yb.pow(2).mean()
+
+
+def _worker_order(rank, world, port, backend, out):
+    """Ranks whose gradients arrive in different orders must still issue their all_reduce calls in bucket order (the old
+    code launched buckets as they filled: same-sized buckets were silently mixed); trigger parameters cut the buckets;
+    a bucket that never fills in an overlapped iteration is an error, as in the reference's epilogue."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    _paths()
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import apex  # noqa: F401
+        _install_cpu_double()
+        from apex.parallel import DistributedDataParallel as DDP
+        import copy
+        torch.manual_seed(5)
+        base = TwoBranch()
+        model = copy.deepcopy(base)
+        ddp = DDP(model, message_size=1)                    # one bucket per parameter
+        for it in range(4):
+            xs = [torch.randn(8, 32, generator=torch.Generator().manual_seed(10 * it + r)) for r in range(world)]
+            want = []
+            for r in range(world):
+                ref = copy.deepcopy(base)
+                ref(xs[r]).backward()
+                want.append([p.grad.clone() for p in ref.parameters()])
+            for p in model.parameters():
+                p.grad = None
+            ddp(xs[rank], a_last=(rank == 1)).backward()    # rank 1 produces a's gradients first, rank 0 b's
+            for i, p in enumerate(model.parameters()):
+                mean = sum(w[i] for w in want) / world
+                assert torch.allclose(p.grad, mean, rtol=1e-5, atol=1e-7), (it, rank, i)
+        assert len(ddp._buckets) == 4 and ddp._num_regular == 4
+        # a regular bucket that does not fill: refused in the epilogue (every rank skips b here, so nobody hangs)
+        for p in model.parameters():
+            p.grad = None
+        try:
+            ddp(torch.randn(8, 32), skip_b=True).backward()
+            raise AssertionError("an unfilled overlapped bucket went unnoticed")
+        except RuntimeError as e:
+            assert "next_bucket" in str(e)
+        # trigger parameters: buckets end where a trigger's gradient arrives (reference :373-376)
+        model = copy.deepcopy(base)
+        ddp = DDP(model, allreduce_trigger_params=[model.b.weight])
+        for it in range(3):
+            xs = [torch.randn(8, 32, generator=torch.Generator().manual_seed(70 * it + r)) for r in range(world)]
+            want = []
+            for r in range(world):
+                ref = copy.deepcopy(base)
+                ref(xs[r]).backward()
+                want.append([p.grad.clone() for p in ref.parameters()])
+            for p in model.parameters():
+                p.grad = None
+            ddp(xs[rank]).backward()
+            for i, p in enumerate(model.parameters()):
+                assert torch.allclose(p.grad, sum(w[i] for w in want) / world, rtol=1e-5, atol=1e-7), (it, rank, i)
+        # rank 0's iteration-1 order is b.bias/b.weight (b evaluated last), then a.*: cut after b.weight -> 2 buckets
+        assert len(ddp._buckets) == 2 and any(p is model.b.weight for p in ddp._buckets[0].params)
+        assert all(p is not model.b.weight for p in ddp._buckets[1].params)
+        out.put((rank, "ok"))
+    except Exception:
+        import traceback
+        out.put((rank, "FAIL: " + traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ddp_bucket_order_and_triggers_world2_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_order, args=(r, 2, 29773, "gloo", q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in results:
+        assert msg == "ok", "rank %d: %s" % (rank, msg)

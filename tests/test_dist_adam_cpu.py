@@ -372,3 +372,123 @@ def test_sharded_adam_matches_unsharded_world2_gloo(K, dtype_name):
         p.join(timeout=60)
     for rank, msg in results:
         assert msg == "ok", "rank %d: %s" % (rank, msg)
+
+
+def _worker_parity_tool(rank, world, port, K, out):
+    """tools/multi_gpu_parity.sharded_adam_parity (the check bench.py's N > 1 arm runs on the GPUs) on gloo with the
+    oracle doubles: it must pass on a correct optimizer and fail when one shard element is corrupted."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    for p in (os.path.join(ROOT, "rocm-apex_b200"), ROOT, os.path.join(ROOT, "tools")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import apex  # noqa: F401
+        _install_kernel_doubles()
+        import multi_gpu_parity as mgp
+        from apex.contrib.optimizers.distributed_fused_adam import DistributedFusedAdam
+        shapes = [(300, 7), (64,), (5,), (1000, 3), (1,), (4096,)]
+
+        def build():
+            g0 = torch.Generator().manual_seed(7)
+            params = [torch.nn.Parameter((torch.randn(s, generator=g0) * 0.1).bfloat16()) for s in shapes]
+            opt = DistributedFusedAdam(params, lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=0.01, dwu_num_blocks=K,
+                                       dwu_num_chunks=1, predivide=False, overlap_reductions=False, zero_copy_params=True)
+            opt.set_global_scale(float(world))
+            flat = opt.attach_flat_grads()
+            flat.copy_(torch.randn(flat.numel(), generator=torch.Generator().manual_seed(100 + rank)))
+            return opt
+
+        res, ok = mgp.sharded_adam_parity(build(), sample_elems=512)
+        assert ok, res
+        assert res["master_p_m_v_max_rel"] == 0.0 and res["copy_vs_unsharded_max_ulp"] == 0
+        assert res["elements_checked"] > 0 and res["reduced_grad_vs_rn_fp32_sum_max_ulp"] <= 1
+        # a wrong update on one rank must be caught: corrupt the optimizer's step kernel for rank 1
+        opt = build()
+        if rank == 1:
+            real = opt._dist_adam.multi_tensor_fused_adam
+
+            def broken(chunk, noop, lists, *a):
+                real(chunk, noop, lists, *a)
+                lists[0][0][0] += 1.0          # first element of the shard's first fragment: inside the head sample
+
+            opt._dist_adam = types.SimpleNamespace(multi_tensor_fused_adam=broken)
+        res, ok = mgp.sharded_adam_parity(opt, sample_elems=512)
+        assert not ok and res["master_p_m_v_max_rel"] > 1e-6, res
+        out.put((rank, "ok"))
+    except Exception:
+        import traceback
+        out.put((rank, "FAIL: " + traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("K", [1, 4])
+def test_bench_parity_tool_world2_gloo(K):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_parity_tool, args=(r, 2, 29640 + K, K, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in results:
+        assert msg == "ok", "rank %d: %s" % (rank, msg)
+
+
+def _worker_overflow_then_clean(rank, world, port, out):
+    """One iteration with a non-finite gradient, then a clean one: the overflow flag of the flatten pass gates the
+    gathered-parameters -> model-parameters copy for THAT iteration only (the reference clears it before every flatten,
+    apex/contrib/optimizers/distributed_fused_adam.py:481); on the clean iteration the model parameters must move."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    for p in (os.path.join(ROOT, "rocm-apex_b200"), ROOT):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import apex  # noqa: F401
+        _install_kernel_doubles()
+        from apex.contrib.optimizers.distributed_fused_adam import DistributedFusedAdam
+        shapes = [(300, 7), (64,), (1000, 3)]
+        g0 = torch.Generator().manual_seed(7)
+        params = [torch.nn.Parameter(torch.randn(s, generator=g0) * 0.1) for s in shapes]
+        opt = DistributedFusedAdam(params, lr=1e-2, betas=(0.9, 0.99), eps=1e-8, dwu_num_blocks=2, dwu_num_chunks=1,
+                                   overlap_reductions=False)
+        opt.set_global_scale(1.0)
+        for it in range(3):
+            gr = torch.Generator().manual_seed(100 * it + rank)
+            grads = [torch.randn(s, generator=gr) for s in shapes]
+            if it == 0 and rank == 1:
+                grads[1][3] = float("inf")
+            for p, g in zip(params, grads):
+                p.grad = g
+            before = [p.detach().clone() for p in params]
+            opt.complete_reductions()
+            opt.step()
+            if it == 0:
+                if rank == 1:       # the rank that saw the inf skips its copy for this iteration, like the reference
+                    assert int(opt._overflow_buf) == 1 and all(torch.equal(a, b.detach()) for a, b in zip(before, params))
+            else:
+                assert int(opt._overflow_buf) == 0, (it, rank)
+                assert not torch.equal(before[0], params[0].detach()), "model parameters stopped following the masters"
+                assert not torch.equal(before[2], params[2].detach())
+        out.put((rank, "ok"))
+    except Exception:
+        import traceback
+        out.put((rank, "FAIL: " + traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_overflow_flag_is_cleared_every_iteration_world2_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_overflow_then_clean, args=(r, 2, 29660, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in results:
+        assert msg == "ok", "rank %d: %s" % (rank, msg)

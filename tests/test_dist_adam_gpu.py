@@ -206,3 +206,81 @@ def test_e5m2_allgather_world2_nccl(K, fused):
         p.join(timeout=60)
     for rank, msg in results:
         assert msg == "ok", "rank %d: %s" % (rank, msg)
+
+
+def _spawn(target, world, args):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=target, args=(r, world) + tuple(args) + (q,)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in results:
+        assert msg == "ok", "rank %d: %s" % (rank, msg)
+
+
+@pytest.mark.parametrize("K,zero_copy", [(1, False), (4, True)])
+def test_sharded_adam_world1_nccl_one_gpu(K, zero_copy):
+    """The same comparison on ONE GPU (a 1-rank NCCL job): no cross-GPU traffic, but the class, the flat layout, the
+    fragment lists, reduce_scatter_tensor / all_gather_into_tensor and every kernel of the step run for real on a box
+    that has a single device."""
+    _spawn(_worker_w1, 1, (29600 + K, K, zero_copy))
+
+
+def _worker_w1(rank, world, port, K, zero_copy, out):
+    _worker(rank, world, port, K, zero_copy, False, out)
+
+
+def _worker_overflow(rank, world, port, out):
+    """An iteration with an inf gradient, then clean ones, with the real kernels: the flatten pass's overflow flag gates
+    the gathered -> model copy for that iteration only (reference distributed_fused_adam.py:481 clears it per flatten)."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    for p in (os.path.join(ROOT, "rocm-apex_b200"), ROOT):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        from apex.contrib.optimizers import DistributedFusedAdam
+        shapes = [(300, 7), (64,), (1000, 3)]
+        g0 = torch.Generator().manual_seed(7)
+        params = [torch.nn.Parameter((torch.randn(s, generator=g0) * 0.1).to(dev).half()) for s in shapes]
+        opt = DistributedFusedAdam(params, lr=1e-2, betas=(0.9, 0.99), eps=1e-8, dwu_num_blocks=2, dwu_num_chunks=1,
+                                   overlap_reductions=False)
+        opt.set_global_scale(1.0)
+        for it in range(3):
+            gr = torch.Generator().manual_seed(100 * it + rank)
+            grads = [torch.randn(s, generator=gr).to(dev).half() for s in shapes]
+            if it == 0 and rank == world - 1:
+                grads[1][3] = float("inf")
+            for p, g in zip(params, grads):
+                p.grad = g
+            before = [p.detach().clone() for p in params]
+            opt.complete_reductions()
+            opt.step()
+            torch.cuda.synchronize()
+            if it == 0:
+                if rank == world - 1:
+                    assert int(opt._overflow_buf) == 1 and all(torch.equal(a, b.detach()) for a, b in zip(before, params))
+            else:
+                assert int(opt._overflow_buf) == 0, (it, rank)
+                assert not torch.equal(before[0], params[0].detach()), "model parameters stopped following the masters"
+                assert not torch.equal(before[2], params[2].detach())
+        out.put((rank, "ok"))
+    except Exception:
+        import traceback
+        out.put((rank, "FAIL: " + traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_overflow_flag_cleared_every_iteration_world1_nccl_one_gpu():
+    _spawn(_worker_overflow, 1, (29610,))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_overflow_flag_cleared_every_iteration_world2_nccl():
+    _spawn(_worker_overflow, 2, (29611,))

@@ -104,7 +104,7 @@ def _worker(rank, world, port, backend, out, group_size=0):
                 gr = torch.Generator().manual_seed(100 * it + r)
                 per_rank.append([torch.randn(s, generator=gr) * 4.0 for s in SHAPES])
             if it == 3:     # one rank produces an inf: every rank must skip, nothing may change, step must not advance
-                per_rank[1][2][0] = float("inf")
+                per_rank[world - 1][2][0] = float("inf")
             for p, g in zip(params, per_rank[rank]):
                 p.grad = g.clone().to(dev)
             before = [p.detach().clone() for p in params]
@@ -232,6 +232,12 @@ def test_sharded_lamb_matches_unsharded_world2_nccl():
 
 
 @pytest.mark.gpu
+def test_sharded_lamb_world1_nccl_one_gpu():
+    """1-rank NCCL job on one GPU: the class, its collectives and both sharded-LAMB kernels against float64 LAMB."""
+    _run("nccl", 29755, world=1)
+
+
+@pytest.mark.gpu
 def test_dist_lamb_kernels_match_oracle():
     _paths()
     import distributed_lamb_cuda as ours
@@ -285,3 +291,104 @@ def test_dist_lamb_kernels_match_oracle():
             ours.multi_tensor_lamb_compute_update_term(65536, one, lists, b1, b2, 1 - b1, bc, step, eps, mode, wd, gscale, gnorm, 1.0, sumsq)
             for l0, l1 in zip(keep, lists):
                 assert all(torch.equal(a, b) for a, b in zip(l0, l1))
+
+
+@pytest.mark.gpu
+def test_dist_lamb_kernels_match_reference_binary():
+    """ops_dist_lamb.cu and oracle/dist_lamb_oracle.py against the reference's own
+    multi_tensor_distopt_lamb_kernel.cu compiled unmodified for sm_100a (oracle/_ref/distributed_lamb_cuda_ref.so,
+    oracle/build_ref.sh): both kernels, fp32 and fp16 gradients (the reference dispatches float / half only,
+    multi_tensor_distopt_lamb_kernel.cu:446-449), both decay modes, clipping on and off, fp32 / fp16 / e5m2-byte
+    parameter copies, and the noop gate.  Tolerances: v (a sum of non-negative terms) pure element-wise 2e-6,
+    m / u / p element-wise 1e-6 plus 1e-6 of the tensor's largest magnitude (cancellation), bytes bit-exact."""
+    _paths()
+    import numpy as np
+    import distributed_lamb_cuda as ours
+    from oracle import dist_lamb_oracle as DL
+    from util import assert_close_rel, assert_rel_pure, load_ref, rel_err_stats
+    refm = load_ref("distributed_lamb_cuda_ref")
+    if refm is None:
+        pytest.skip("oracle/_ref/distributed_lamb_cuda_ref.so not built")
+    sizes = [1, 3, 555, 65537, 33333, 8192, 262144, 4]
+    T = len(sizes)
+    g = torch.Generator(device="cuda").manual_seed(71)
+
+    def mk(dt, s=1.0, pos=False):
+        out = []
+        for n in sizes:
+            x = torch.randn(n, generator=g, device="cuda") * s
+            out.append((x.abs() if pos else x).to(dt))
+        return out
+
+    worst = {}
+    for gdt in (torch.float16, torch.float32):
+        for mode in (0, 1):
+            for max_norm in (1.0, 0.0):
+                lists = [mk(gdt, 64.0), mk(torch.float32, 0.1), mk(torch.float32, 0.01), mk(torch.float32, 0.001, True),
+                         mk(torch.float32)]
+                rl = [[t.clone() for t in l] for l in lists]
+                cl = [[t.cpu().clone() for t in l] for l in lists]
+                b1 = torch.linspace(0.85, 0.95, T, device="cuda"); b2 = torch.linspace(0.98, 0.999, T, device="cuda")
+                bc = torch.tensor([1, 0] * (T // 2), device="cuda", dtype=torch.int32)
+                eps = torch.full((T,), 1e-6, device="cuda"); wd = torch.tensor([0.0, 0.01] * (T // 2), device="cuda")
+                step = torch.tensor([3], device="cuda", dtype=torch.int32)
+                gscale, gnorm = torch.tensor([64.0], device="cuda"), torch.tensor([640.0], device="cuda")
+                flag, rflag = (torch.zeros(1, dtype=torch.int32, device="cuda") for _ in range(2))
+                ours.multi_tensor_lamb_compute_update_term(65536, flag, lists, b1, b2, 1 - b1, bc, step, eps, mode, wd, gscale,
+                                                           gnorm, max_norm)
+                refm.multi_tensor_lamb_compute_update_term(65536, rflag, rl, b1, b2, 1 - b1, bc, step, eps, mode, wd, gscale,
+                                                           gnorm, max_norm)
+                DL.compute_update_term([0], cl, b1.tolist(), b2.tolist(), bc.tolist(), 3, eps.tolist(), mode, wd.tolist(), 64.0,
+                                       640.0, max_norm)
+                assert int(flag) == int(rflag) == 0
+                for a, b in zip(lists[0], rl[0]):
+                    assert torch.equal(a, b)                 # gradients are inputs only in both
+                assert_rel_pure(lists[3], rl[3], 2e-6, "stage1 v vs reference binary")
+                assert_rel_pure([t.cuda() for t in cl[3]], rl[3], 2e-6, "oracle v vs reference binary")
+                for k, name in ((2, "m"), (4, "u")):
+                    for a, b, c in zip(lists[k], rl[k], cl[k]):
+                        assert_close_rel(a, b, rtol=1e-6, scale="self", what="stage1 %s vs reference binary" % name)
+                        assert_close_rel(c.cuda(), b, rtol=2e-6, scale="self", what="oracle %s vs reference binary" % name)
+                for k, name in ((2, "m"), (3, "v"), (4, "u")):
+                    mx, p999, _ = rel_err_stats(lists[k], rl[k], floor=1e-12)
+                    worst[name] = max(worst.get(name, 0.0), p999)
+                # stage 2 on the reference's update, so that both sides start from identical inputs
+                for cdt in (torch.float16, torch.uint8, torch.float32):
+                    for nvlamb in (False, True):
+                        u = [t.clone() for t in rl[4]]
+                        p, rp = [t.clone() for t in rl[1]], [t.clone() for t in rl[1]]
+                        pc, rpc = ([torch.zeros(n, dtype=cdt, device="cuda") for n in sizes] for _ in range(2))
+                        pn = torch.linspace(1.0, 2.0, T, device="cuda"); un = torch.linspace(0.5, 3.0, T, device="cuda")
+                        un[2] = 0.0                                                       # zero norm: plain lr
+                        off = torch.tensor(list(reversed(range(T))), device="cuda", dtype=torch.int64)
+                        lrt = torch.tensor([1e-2], device="cuda")
+                        ours.multi_tensor_lamb_update_weights(65536, flag, [u, p, pc], pn, un, off, lrt, wd, gnorm, nvlamb)
+                        refm.multi_tensor_lamb_update_weights(65536, rflag, [[t.clone() for t in u], rp, rpc], pn, un, off, lrt,
+                                                              wd, gnorm, nvlamb)
+                        for a, b in zip(p, rp):
+                            assert_close_rel(a, b, rtol=1e-6, scale="self", what="stage2 p vs reference binary")
+                        for a, b, pa_ in zip(pc, rpc, p):
+                            if cdt == torch.uint8:
+                                # bytes: equal wherever the two fp32 results are (they may differ in the last bit of p)
+                                assert np.array_equal(a.cpu().numpy(), O_pack(pa_))
+                            elif cdt == torch.float16:
+                                assert_close_rel(a, b, rtol=1e-3, scale="self", what="stage2 fp16 copy vs reference binary")
+                            else:
+                                assert_close_rel(a, b, rtol=1e-6, scale="self", what="stage2 fp32 copy vs reference binary")
+                        if cdt == torch.uint8:
+                            # and the reference's own bytes are the same packing of ITS fp32 result
+                            for b, pr in zip(rpc, rp):
+                                assert np.array_equal(b.cpu().numpy(), O_pack(pr))
+                # noop gate: flag == 1 -> neither implementation moves anything
+                keep = [[t.clone() for t in l] for l in lists]
+                one = torch.ones(1, dtype=torch.int32, device="cuda")
+                ours.multi_tensor_lamb_compute_update_term(65536, one, lists, b1, b2, 1 - b1, bc, step, eps, mode, wd, gscale, gnorm, max_norm)
+                refm.multi_tensor_lamb_compute_update_term(65536, one, rl, b1, b2, 1 - b1, bc, step, eps, mode, wd, gscale, gnorm, max_norm)
+                for l0, l1 in zip(keep, lists):
+                    assert all(torch.equal(a, b) for a, b in zip(l0, l1))
+    print("dist LAMB vs reference binary, 99.9th-percentile relative error: %s" % worst)
+
+
+def O_pack(t):
+    from oracle import mt_oracle as O
+    return O.pack_e5m2(t.detach().cpu().numpy())

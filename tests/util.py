@@ -1,4 +1,5 @@
 """Shared helpers for the parity tests."""
+import math
 import os
 import sys
 
@@ -63,3 +64,42 @@ def assert_close_rel(a, b, rtol, atol=0.0, what="", scale=None):
 def resnet50_shapes():
     import param_shapes
     return param_shapes.resnet50()
+
+
+def rel_err_stats(a, b, floor=0.0):
+    """Element-wise relative error |a-b|/|b| in fp64 over the elements where b is finite and |b| > floor:
+    (max, 99.9th percentile, number of elements).  Works on lists of tensors (concatenated)."""
+    if isinstance(a, (list, tuple)):
+        a = torch.cat([t.detach().reshape(-1).double() for t in a])
+        b = torch.cat([t.detach().reshape(-1).double() for t in b])
+    else:
+        a, b = a.detach().reshape(-1).double(), b.detach().reshape(-1).double()
+    keep = torch.isfinite(b) & (b.abs() > floor)
+    if not bool(keep.any()):
+        return 0.0, 0.0, 0
+    r = (a[keep] - b[keep]).abs() / b[keep].abs()
+    n = r.numel()
+    sub = r if n <= (1 << 24) else r[:: (n >> 24) + 1]      # the percentile of very long lists comes from a strided sample
+    p999 = float(torch.kthvalue(sub, max(1, int(math.ceil(0.999 * sub.numel()))))[0])
+    return float(r.max()), p999, n
+
+
+def assert_rel_pure(a, b, rtol, what="", tiny=0.0):
+    """Pure element-wise relative bound |a-b| <= rtol*|b| (+ tiny absolute, for flushed denormals only):
+    for quantities that are sums of non-negative terms (second moments, norms, trust ratios) there is no
+    cancellation to excuse anything looser."""
+    if isinstance(a, (list, tuple)):
+        for i, (x, y) in enumerate(zip(a, b)):
+            assert_rel_pure(x, y, rtol, "%s[%d]" % (what, i), tiny)
+        return
+    a64, b64 = a.detach().double().reshape(-1), b.detach().double().reshape(-1)
+    assert a64.shape == b64.shape, what
+    fin = torch.isfinite(b64)
+    assert torch.equal(torch.isfinite(a64), fin), "%s: finiteness differs" % what
+    err = (a64[fin] - b64[fin]).abs()
+    bad = err > (rtol * b64[fin].abs() + tiny)
+    if bool(bad.any()):
+        i = int(torch.nonzero(bad)[0])
+        raise AssertionError("%s: %d/%d elements outside pure rtol=%g; first: got %r want %r (rel %.3g)" % (
+            what, int(bad.sum()), err.numel(), rtol, float(a64[fin][i]), float(b64[fin][i]),
+            float(err[i] / b64[fin][i].abs().clamp_min(1e-300))))
