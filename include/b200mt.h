@@ -45,6 +45,7 @@ typedef struct b200mt_lists {
   int32_t            depth;
   int32_t            dtype[B200MT_MAX_DEPTH];
   int32_t            device; /* CUDA device ordinal the tensors live on               */
+  const struct b200mt_prepared* prepared; /* NULL, or a handle of b200mt_lists_prepare for exactly this list set */
 } b200mt_lists;
 
 /* ---- library ---------------------------------------------------------------------------- */
@@ -237,6 +238,31 @@ int b200mt_maybe_adam_undo(const b200mt_lists* lists, int chunk_size, const int3
                            float beta1, float beta2, float eps, float grad_scale, int step, int mode,
                            int bias_correction, float decay, void* stream);
 
+/* ---- prepared list sets -- no counterpart in the reference, whose harness re-packs the tensor addresses into kernel
+ * arguments on every call (csrc/multi_tensor_apply.cuh:84-146: the cost this removes).
+ * By default every entry point rebuilds the descriptor-table image of its list set, hashes it and compares it with the
+ * cached copy: O(depth * ntensors) host work per call, which for lists of thousands of small tensors is longer than the
+ * kernel.  A host that KNOWS its tensors stay where they are (optimizer state, flat gradient views, bucket buffers)
+ * can prepare the list set once and pass the handle in lists->prepared on every call: the library then uses the
+ * handle's resident table directly -- no image, no hash, no compare.  ptrs / numel / ntensors / depth / dtype / device
+ * must still describe the same list set (ntensors, depth and device are checked against the handle; the pointers are
+ * NOT re-read: moving a tensor without preparing again is the caller's bug).  One handle serves every op: the table
+ * for a kind of op (element-wise, norm-type per chunk size) is uploaded on the handle's first use with it, on that
+ * call's stream.  b200mt_lists_release frees the tables (it may wait for the device). */
+typedef struct b200mt_prepared b200mt_prepared;
+int b200mt_lists_prepare(const b200mt_lists* lists, b200mt_prepared** out);
+int b200mt_lists_release(b200mt_prepared* handle);
+
+/* ---- launch trace -- no counterpart in the reference (its profiling hook is apex.pyprof's NVTX wrapper around
+ * fused_adam_cuda.adam, apex/pyprof/examples/apex/fused_adam.py:6-7).  Between b200mt_trace_begin(max) and
+ * b200mt_trace_end every kernel this library launches is bracketed by two CUDA events on its stream (and launched
+ * without programmatic early start, so the pair sees the whole kernel).  trace_end waits for the recorded events and
+ * returns the durations in launch order; b200mt_trace_name(i) names launch i (the demangled kernel functor).  Events
+ * are created in trace_begin: call it outside stream capture and outside timed regions. */
+int b200mt_trace_begin(int max_launches);
+int b200mt_trace_end(float* ms, int capacity, int* count);
+const char* b200mt_trace_name(int i);
+
 /* ---- b200mt_l2norm_flat_noalloc -- no counterpart in the reference.
  * L2 norm of ONE flat device buffer (x, dtype, numel) with the same two-pass arithmetic and the same
  * per-chunk overflow flag as b200mt_l2norm, for hosts that cannot let this library allocate: a
@@ -246,14 +272,18 @@ int b200mt_maybe_adam_undo(const b200mt_lists* lists, int chunk_size, const int3
  * working memory is a fixed array inside the library image:
  *   - B200MT_NOALLOC_SCRATCH_BYTES of device memory are held on every GPU that loads the library,
  *     until the process exits;
- *   - inputs that need more than B200MT_NOALLOC_MAX_TILES scheduling tiles are refused with an error
- *     (1,073,741,824 elements with chunk_size >= 16384: this entry point always tiles by 16384
- *     elements; fewer for smaller chunk sizes -- at least one tile per chunk);
+ *   - inputs that need more than B200MT_NOALLOC_MAX_TILES scheduling tiles are refused with an error.
+ *     The limit counts tiles: every chunk of chunk_size elements is cut into ceil(chunk_size / 16384)
+ *     equal tiles, so numel elements need floor(numel / chunk_size) * ceil(chunk_size / 16384) tiles
+ *     plus those of the last partial chunk.  65536 tiles are 1,073,741,824 elements only when
+ *     chunk_size is a multiple of 16384 (the default 65536 is); chunk_size 16400 -> 2 tiles per
+ *     chunk -> 537,395,200 elements; chunk_size < 16384 -> one tile per chunk -> 65536 * chunk_size;
  *   - all calls on a device share the array: calls whose GPU work may overlap (unordered streams)
  *     race and must be ordered by the caller; back-to-back calls on one stream are safe, the
  *     function re-zeroes what has to start at zero;
  *   - the first call on each device queries the array's device address (host-side, nothing is
- *     allocated): make that call before starting any stream capture on that device.
+ *     allocated) and caches it: make that call before starting any stream capture on that device;
+ *     the cached address does not survive cudaDeviceReset() / a context teardown.
  * ret: device float[1].  *noop is set when a chunk's sum of squares is inf/NaN. */
 #define B200MT_NOALLOC_MAX_TILES 65536
 #define B200MT_NOALLOC_SCRATCH_BYTES (512 + 4 * (B200MT_NOALLOC_MAX_TILES + 2) + 248)

@@ -13,6 +13,7 @@
 # (-O3 --use_fast_math -lineinfo + the VERSION_GE_* macros, setup.py:145-154) plus the four
 # -D__CUDA_NO_HALF*/BFLOAT16* defines torch's CUDAExtension adds to every nvcc line (without them
 # multi_tensor_distopt_lamb_kernel.cu:352 meets an ambiguous operator!= on at::Half).
+#   pyref/apex/**.py           <- the reference's Python package, staged unmodified (tests run it over both back ends)
 # Only tests/, __graft_entry__.smoke() and bench.py's comparison legs may load these.
 set -euo pipefail
 REF=${REF:-/root/reference}
@@ -74,3 +75,19 @@ build_module distributed_lamb_cuda_ref \
   $REF/apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb.cpp \
   $REF/apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb_kernel.cu
 rm -rf "$OBJ"
+
+# The reference's own Python (apex/**/*.py, unmodified, .py files only) staged next to the compiled checkers, so that
+# tests/test_reference_python_gpu.py can run the reference's optimizer / amp classes on the GPU box -- once over this
+# repo's amp_C shim and once over amp_C_ref -- and compare.  oracle/_ref/ is git-ignored: nothing of it enters the history.
+if [ ! -d "$OUT/pyref/apex" ] || [ -n "${FORCE:-}" ]; then
+  rm -rf "$OUT/pyref"
+  mkdir -p "$OUT/pyref"
+  (cd "$REF" && find apex -name '*.py' | while read -r f; do mkdir -p "$OUT/pyref/$(dirname "$f")"; cp "$f" "$OUT/pyref/$f"; done)
+  # ... and the reference's own unit tests for this path (tests/L0/run_amp, tests/L0/run_optimizers), to be run over both back ends
+  mkdir -p "$OUT/pyref_tests"
+  for d in run_amp run_optimizers; do
+    mkdir -p "$OUT/pyref_tests/$d"
+    cp "$REF"/tests/L0/$d/*.py "$OUT/pyref_tests/$d/"
+  done
+  echo "[oracle/build_ref] staged $(find "$OUT/pyref" -name '*.py' | wc -l) reference .py files under $OUT/pyref"
+fi

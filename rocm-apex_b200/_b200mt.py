@@ -39,6 +39,7 @@ class Lists(ctypes.Structure):
         ("depth", ctypes.c_int32),
         ("dtype", ctypes.c_int32 * MAX_DEPTH),
         ("device", ctypes.c_int32),
+        ("prepared", ctypes.c_void_p),
     ]
 
 
@@ -58,6 +59,11 @@ def _load():
         "b200mt_table_hits": (ctypes.c_int64, []),
         "b200mt_set_tuning": (c_int, [c_int, c_int]),
         "b200mt_shutdown": (c_int, []),
+        "b200mt_lists_prepare": (c_int, [LP, ctypes.POINTER(ctypes.c_void_p)]),
+        "b200mt_lists_release": (c_int, [vp]),
+        "b200mt_trace_begin": (c_int, [c_int]),
+        "b200mt_trace_end": (c_int, [vp, c_int, vp]),
+        "b200mt_trace_name": (ctypes.c_char_p, [c_int]),
         "b200mt_scale": (c_int, [LP, c_int, vp, c_float, vp]),
         "b200mt_axpby": (c_int, [LP, c_int, vp, c_float, c_float, c_int, vp]),
         "b200mt_l2norm": (c_int, [LP, c_int, vp, vp, vp, c_int, vp]),
@@ -108,6 +114,25 @@ if os.environ.get("B200MT_PY_PACK"):
     _fast_pack = None
 
 
+class trace(object):
+    """with trace() as t: ...; t.launches -> [(kernel name, ms)] for every kernel the library launched inside the block
+    (b200mt_trace_begin / _end: events around each launch; PDL off while tracing)."""
+
+    def __init__(self, max_launches=4096):
+        self.max, self.launches = max_launches, []
+
+    def __enter__(self):
+        check(lib.b200mt_trace_begin(self.max))
+        return self
+
+    def __exit__(self, *exc):
+        ms = (ctypes.c_float * self.max)()
+        n = ctypes.c_int(0)
+        check(lib.b200mt_trace_end(ms, self.max, ctypes.byref(n)))
+        self.launches = [(lib.b200mt_trace_name(i).decode(), float(ms[i])) for i in range(min(n.value, self.max))]
+        return False
+
+
 def check(rc):
     """Turn a non-zero C return code into the RuntimeError the reference's TORCH_CHECK would raise."""
     if rc != 0:
@@ -144,14 +169,63 @@ class RawBuffer(object):
 
 class Packed(object):
     """A tensor-list set in C-ABI form.  Keeps the numpy arrays alive for the duration of the call."""
-    __slots__ = ("struct", "ptrs", "numel", "device", "ntensors", "depth")
+    __slots__ = ("struct", "ptrs", "numel", "device", "ntensors", "depth", "handle", "keep", "__weakref__")
 
     def ref(self):
         return ctypes.byref(self.struct)
 
 
+class Prepared(Packed):
+    """A list set prepared once (b200mt_lists_prepare): every drop-in entry point accepts it in place of
+    `tensor_lists` and then skips the per-call walk of the lists, the table image, its hash and the compare -- what
+    is left of a call is the launch.  The caller promises that the tensors stay at their addresses and sizes for the
+    life of the object (it keeps the tensor objects alive, so freed storage cannot be reused under it; re-pointing a
+    tensor with `.data =` / `set_()` / `resize_()` is the one thing that breaks the promise).  release() or garbage
+    collection frees the device tables."""
+    __slots__ = ()
+
+    def __len__(self):             # quacks like the list of lists it was made from
+        return self.depth
+
+    def __getitem__(self, d):
+        return self.keep[d]
+
+    def release(self):
+        h, self.handle = getattr(self, "handle", None), None
+        if h:
+            self.struct.prepared = None
+            lib.b200mt_lists_release(h)
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
+
+
+def prepare(tensor_lists):
+    """-> Prepared: validate and pack `tensor_lists` once, keep a resident descriptor table for them."""
+    p = pack(tensor_lists)
+    q = Prepared()
+    for name in ("struct", "ptrs", "numel", "device", "ntensors", "depth"):
+        setattr(q, name, getattr(p, name))
+    q.keep = [list(l) for l in tensor_lists]          # the tensors stay alive as long as the handle does
+    h = ctypes.c_void_p()
+    check(lib.b200mt_lists_prepare(q.ref(), ctypes.byref(h)))
+    q.handle = h.value
+    q.struct.prepared = h.value
+    return q
+
+
 def pack(tensor_lists, depth=None):
-    """Validate `tensor_lists` like csrc/multi_tensor_apply.cuh:53-70 and build the C descriptor."""
+    """Validate `tensor_lists` like csrc/multi_tensor_apply.cuh:53-70 and build the C descriptor.
+    A `Prepared` list set passes straight through (only its depth is checked)."""
+    if isinstance(tensor_lists, Packed):
+        if depth is not None:
+            ok = (tensor_lists.depth in depth) if isinstance(depth, (tuple, list)) else (tensor_lists.depth == depth)
+            if not ok:
+                raise RuntimeError("tensor_lists.size() != depth")
+        return tensor_lists
     nlists = len(tensor_lists)
     if depth is not None:
         ok = (nlists in depth) if isinstance(depth, (tuple, list)) else (nlists == depth)

@@ -12,6 +12,8 @@ import torch
 
 import _b200mt as _mt
 
+prepare = _mt.prepare     # extension: amp_C.prepare(tensor_lists) -> a handle every function below accepts as `tensor_lists`
+
 __all__ = [
     "multi_tensor_scale", "multi_tensor_axpby", "multi_tensor_l2norm", "multi_tensor_l2norm_mp",
     "multi_tensor_l2norm_scale", "multi_tensor_adam", "multi_tensor_sgd", "multi_tensor_lamb",
@@ -38,7 +40,7 @@ def multi_tensor_axpby(chunk_size, noop_flag, tensor_lists, a, b, arg_to_check):
 
 def _l2norm(chunk_size, noop_flag, tensor_lists, per_tensor, flags):
     L = _mt.pack(tensor_lists, 1)
-    dev = tensor_lists[0][0].device
+    dev = torch.device("cuda", L.device)
     ret = torch.empty(1, dtype=torch.float32, device=dev)
     per = torch.empty(L.ntensors if per_tensor else 0, dtype=torch.float32, device=dev)
     _mt.check(_lib.b200mt_l2norm(L.ref(), int(chunk_size), _mt.noop_ptr(noop_flag), ret.data_ptr(),
@@ -60,7 +62,7 @@ def multi_tensor_l2norm_mp(chunk_size, noop_flag, tensor_lists, per_tensor_pytho
 def multi_tensor_l2norm_scale(chunk_size, noop_flag, tensor_lists, scale, per_tensor_python=None):
     """Norm of `in` plus out = in*scale in one pass (csrc/multi_tensor_l2norm_scale_kernel.cu:258-324)."""
     L = _mt.pack(tensor_lists, 2)
-    dev = tensor_lists[0][0].device
+    dev = torch.device("cuda", L.device)
     per_tensor = bool(per_tensor_python)
     ret = torch.empty(1, dtype=torch.float32, device=dev)
     per = torch.empty(L.ntensors if per_tensor else 0, dtype=torch.float32, device=dev)

@@ -91,7 +91,7 @@ def initialize(models, optimizers=None, enabled=True, opt_level="O1", cast_model
     props.patch_torch_functions = ac is not None
     props.keep_batchnorm_fp32, props.master_weights, props.loss_scale = kbn, mw, ls
     if cast_model_type is not None:
-        props.cast_model_type = cast_model_type
+        props.cast_model_type = cast_model_type or None      # False = "leave the model alone" (reference frontend.py:65-77)
     if keep_batchnorm_fp32 is not None:
         props.keep_batchnorm_fp32 = keep_batchnorm_fp32 if not isinstance(keep_batchnorm_fp32, str) else keep_batchnorm_fp32 == "True"
     if master_weights is not None:

@@ -38,14 +38,41 @@ struct TileLoc {
   int       len;     // elements in the tile
 };
 
-__device__ __forceinline__ TileLoc locate_tile(const TableView& tv, int tile) {
-  // upper_bound(tile_prefix, tile) - 1 : last tensor whose first tile is <= tile.  Empty tensors
-  // have zero tiles and can never be selected.
-  int lo = 0, hi = tv.ntensors;  // invariant: prefix[lo] <= tile < prefix[hi]
+#ifndef B200MT_WARP_SEARCH
+#define B200MT_WARP_SEARCH 1   // 0: plain binary search (log2 T dependent loads), 1: 32-way warp search (log33 T rounds)
+#endif
+
+// Last tensor whose first tile is <= tile (upper_bound(tile_prefix, tile) - 1).  Empty tensors have zero tiles
+// and can never be selected.  Must be called by all 32 lanes of a warp with the same arguments.
+//
+// The look-up is the prologue of every CTA: nothing of the tile can be requested before it is known, and a binary
+// search is a chain of log2(T) DEPENDENT loads (8 for the ResNet-50 list, 14 for 10,000 tensors), each an L1/L2 round
+// trip during which the CTA's slot moves no data.  Here the 32 lanes probe 32 evenly spaced entries at once and a
+// ballot picks the sub-range: ceil(log33 T) rounds (2 up to 1,089 tensors, 3 up to 35,937).
+__device__ __forceinline__ int find_tensor(const int* __restrict__ prefix, int ntensors, int tile) {
+  int lo = 0, hi = ntensors;  // invariant: prefix[lo] <= tile < prefix[hi]
+#if B200MT_WARP_SEARCH
+  const int lane = threadIdx.x & 31;
+  while (hi - lo > 1) {
+    const long long span = hi - lo;
+    const int idx = lo + (int)(((lane + 1) * span) / 33);          // in [lo, hi - 1], non-decreasing in lane
+    const bool le = __ldg(prefix + idx) <= tile;                    // true for a leading run of lanes (prefix is sorted)
+    const int c = __popc(__ballot_sync(0xffffffffu, le));
+    const int nlo = c ? lo + (int)((c * span) / 33) : lo;           // probe of the last lane that said "<="
+    const int nhi = (c < 32) ? lo + (int)(((c + 1) * span) / 33) : hi;   // probe of the first lane that said ">"
+    lo = nlo; hi = nhi;
+  }
+#else
   while (hi - lo > 1) {
     int mid = (lo + hi) >> 1;
-    if (__ldg(tv.tile_prefix + mid) <= tile) lo = mid; else hi = mid;
+    if (__ldg(prefix + mid) <= tile) lo = mid; else hi = mid;
   }
+#endif
+  return lo;
+}
+
+__device__ __forceinline__ TileLoc locate_tile(const TableView& tv, int tile) {
+  const int lo = find_tensor(tv.tile_prefix, tv.ntensors, tile);
   TileLoc L;
   L.tensor = lo;
   const int local = tile - __ldg(tv.tile_prefix + lo);
@@ -668,6 +695,28 @@ __device__ __forceinline__ void adam_rule(float gin, float& p, float& m, float& 
     p = p - lr * (fast_div(mu, denom) + decay * p);
   }
 }
+
+// CTAs per SM the light streaming ops (scale, axpby, cast, the norm passes: ~20 live registers) are compiled for.
+// ncu on the ResNet-50 unscale showed 44.7 % warps active with the register cap of 4 CTAs/SM of round 1
+// (profiles/adam_scale_r01_raw.csv).  Swept per op on B200 with the L2 flushed (profiles/sweep_light_r02.txt):
+//   scale / axpby   8 CTAs/SM (32 registers): 1000x64K scale 112.5 -> 88.1 us, axpby 149.5 -> 129.1 us
+//   fp32 norms      6 CTAs/SM (42 registers; 8 spills the 16 accumulating registers): 1000x64K l2norm 72.7 -> 60.5 us
+//   16-bit norms    4 CTAs/SM (one 128-bit load per thread in flight is enough; more CTAs only add tile prologues)
+// B200MT_LIGHT_MIN_CTAS, when defined, overrides all of them (the sweep builds).
+#ifdef B200MT_LIGHT_MIN_CTAS
+#define B200MT_SCALE_MIN_CTAS B200MT_LIGHT_MIN_CTAS
+#define B200MT_NORM32_MIN_CTAS B200MT_LIGHT_MIN_CTAS
+#define B200MT_NORM16_MIN_CTAS B200MT_LIGHT_MIN_CTAS
+#endif
+#ifndef B200MT_SCALE_MIN_CTAS
+#define B200MT_SCALE_MIN_CTAS 8
+#endif
+#ifndef B200MT_NORM32_MIN_CTAS
+#define B200MT_NORM32_MIN_CTAS 6
+#endif
+#ifndef B200MT_NORM16_MIN_CTAS
+#define B200MT_NORM16_MIN_CTAS 4
+#endif
 
 // Default no-op hooks an Op can inherit.
 struct OpBase {

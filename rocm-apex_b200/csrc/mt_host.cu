@@ -5,6 +5,7 @@
 #include <climits>
 #include <cstdlib>
 #include <cstring>
+#include <cxxabi.h>
 #include <map>
 #include <mutex>
 #include <vector>
@@ -57,6 +58,32 @@ static void init_tuning() {
   if (const char* e = getenv("B200MT_NORM_TILE_ELEMS")) { int v = atoi(e); if (v >= 64) g_norm_tile_elems = v; }
 }
 
+// ---- launch trace -----------------------------------------------------------------------------------------------
+namespace {
+struct TraceRec { cudaEvent_t a = nullptr, b = nullptr; std::string name; };
+std::vector<TraceRec> g_trace;      // pre-created event pairs
+size_t g_trace_used = 0;
+std::atomic<bool> g_tracing{false};
+}  // namespace
+
+bool trace_on() { return g_tracing.load(std::memory_order_relaxed); }
+
+void trace_before(cudaStream_t stream, const char* mangled) {
+  if (g_trace_used >= g_trace.size()) return;       // capacity reached: later launches go unrecorded
+  TraceRec& r = g_trace[g_trace_used];
+  int st = 0;
+  char* dem = abi::__cxa_demangle(mangled, nullptr, nullptr, &st);
+  r.name = (st == 0 && dem) ? dem : mangled;
+  free(dem);
+  cudaEventRecord(r.a, stream);
+}
+
+void trace_after(cudaStream_t stream) {
+  if (g_trace_used >= g_trace.size()) return;
+  cudaEventRecord(g_trace[g_trace_used].b, stream);
+  g_trace_used++;
+}
+
 bool pdl_enabled() {
   init_tuning();
   return g_pdl;
@@ -102,7 +129,9 @@ struct Slot {
   char* host = nullptr;  // pinned shadow of the image
   char* dev = nullptr;
   cudaEvent_t uploaded = nullptr;
-  std::vector<cudaStream_t> users;  // streams that may still be reading `dev`
+  std::vector<cudaStream_t> users;    // streams already ordered after the upload (emptied once the upload is known complete)
+  std::vector<cudaStream_t> readers;  // distinct streams whose kernels may still read `dev` (consulted on eviction; bounded by
+                                      // the number of streams the process uses, reset when the slot is refilled)
   uint64_t tick = 0;
   bool upload_done = false;  // the upload has been seen complete from the host: no stream needs to wait for it
   bool pinned = false;       // used while a stream was capturing: a CUDA graph holds `dev`, never evict
@@ -188,30 +217,30 @@ int check_common(const b200mt_lists* L, int chunk_size) {
   return 0;
 }
 
-int acquire_table(const b200mt_lists* L, int dmin, int dmax, const Tiling& tiling,
-                  cudaStream_t stream, TableView* out) {
-  B200MT_CHECK(L->depth >= dmin && L->depth <= dmax, "tensor_lists.size() != depth");
-  const int T = L->ntensors, D = L->depth;
-  DevCtx* ctx = ctx_for_current_device(L->device);
+namespace {
 
-  // ---- build the image in host staging memory
-  const size_t off_ptrs = sizeof(ImageHeader);
-  const size_t off_numel = off_ptrs + (size_t)D * T * 8;
-  const size_t off_prefix = off_numel + (size_t)T * 8;
-  const size_t bytes = align_up(off_prefix + (size_t)(T + 1) * 4, 16);
-  if (g_staging.size() < bytes) g_staging.resize(bytes);
+struct ImageLayout { size_t off_ptrs, off_numel, off_prefix, bytes; long long ntiles; };
+
+// Builds the table image for (ptrs, numel) under `tiling` in the calling thread's staging buffer.
+int build_image(const void* const* ptrs, const int64_t* numel, int D, int T, const Tiling& tiling, ImageLayout* lay,
+                char** image) {
+  lay->off_ptrs = sizeof(ImageHeader);
+  lay->off_numel = lay->off_ptrs + (size_t)D * T * 8;
+  lay->off_prefix = lay->off_numel + (size_t)T * 8;
+  lay->bytes = align_up(lay->off_prefix + (size_t)(T + 1) * 4, 16);
+  if (g_staging.size() < lay->bytes) g_staging.resize(lay->bytes);
   char* img = g_staging.data();
-  memset(img + off_prefix, 0, bytes - off_prefix);
-  memcpy(img + off_ptrs, L->ptrs, (size_t)D * T * 8);
-  memcpy(img + off_numel, L->numel, (size_t)T * 8);
-  int* prefix = reinterpret_cast<int*>(img + off_prefix);
+  memset(img + lay->off_prefix, 0, lay->bytes - lay->off_prefix);
+  memcpy(img + lay->off_ptrs, ptrs, (size_t)D * T * 8);
+  memcpy(img + lay->off_numel, numel, (size_t)T * 8);
+  int* prefix = reinterpret_cast<int*>(img + lay->off_prefix);
   long long acc = 0;
   for (int t = 0; t < T; t++) {
-    const long long n = L->numel[t];
+    const long long n = numel[t];
     B200MT_CHECK(n >= 0, "negative numel for tensor %d", t);
     if (n > 0)
       for (int d = 0; d < D; d++)
-        B200MT_CHECK(L->ptrs[(size_t)d * T + t] != nullptr, "NULL data pointer (list %d, tensor %d)", d, t);
+        B200MT_CHECK(ptrs[(size_t)d * T + t] != nullptr, "NULL data pointer (list %d, tensor %d)", d, t);
     prefix[t] = (int)acc;
     const long long full = n / tiling.chunk_elems, rem = n % tiling.chunk_elems;
     acc += full * tiling.ppc + (rem + tiling.tile_elems - 1) / tiling.tile_elems;
@@ -222,6 +251,143 @@ int acquire_table(const b200mt_lists* L, int dmin, int dmax, const Tiling& tilin
   h->magic = 0xb200;
   h->depth = D; h->ntensors = T; h->tile_elems = tiling.tile_elems; h->ppc = tiling.ppc;
   h->ntiles = (uint32_t)acc; h->chunk_elems = tiling.chunk_elems;
+  lay->ntiles = acc;
+  *image = img;
+  return 0;
+}
+
+// A resident table is about to be used on `stream`: order the stream after the upload if it has not been seen
+// complete yet (first use on this stream), pin the slot while a capture refers to it.
+int attach_stream(Slot* slot, cudaStream_t stream, bool capturing) {
+  // the upload is followed by a 4-byte copy of the table's magic word back into pinned memory: seeing it there
+  // proves the upload is over without any CUDA call (none that queries or waits is safe while capturing)
+  if (!slot->upload_done && *slot_ack(slot) == kMagic) slot->upload_done = true;
+  if (slot->upload_done) {
+    slot->users.clear();          // nobody has to be ordered after the upload any more: no need to remember streams
+  } else {
+    bool known = false;
+    for (cudaStream_t u : slot->users) known = known || (u == stream);
+    if (!known) {  // first use on this stream: order after the upload
+      B200MT_CHECK(!capturing, "stream capture: the upload of this tensor list's descriptor table is still in flight on "
+                               "another stream; synchronise before capturing");
+      B200MT_CUDA(cudaStreamWaitEvent(stream, slot->uploaded, 0));
+      slot->users.push_back(stream);
+    }
+  }
+  if (capturing) slot->pinned = true;
+  return 0;
+}
+
+// (Re)fills `slot` with `img` and uploads it on `stream`.  The slot must not be in use by kernels of other streams
+// (the LRU path orders `stream` after them before calling this; a prepared handle's slot is fresh).
+int upload_slot(DevCtx* ctx, Slot* slot, const char* img, size_t bytes, uint64_t hash, cudaStream_t stream) {
+  if (!slot->uploaded) B200MT_CUDA(cudaEventCreateWithFlags(&slot->uploaded, cudaEventDisableTiming));
+  slot->valid = false;
+  slot->upload_done = false;
+  slot->users.clear();
+  slot->readers.clear();
+  if (slot->cap < bytes + kAckBytes) {
+    // Growing: the old device buffer may be read by kernels on this stream -> retire, don't free.
+    if (slot->dev) ctx->retired.push_back(slot->dev);
+    if (slot->host) cudaFreeHost(slot->host);
+    slot->host = slot->dev = nullptr; slot->cap = 0;
+    size_t cap = 16384;
+    while (cap < bytes + kAckBytes) cap *= 2;     // the last kAckBytes of the pinned shadow hold the upload acknowledgement
+    B200MT_CUDA(cudaHostAlloc((void**)&slot->host, cap, cudaHostAllocDefault));
+    B200MT_CUDA(cudaMalloc((void**)&slot->dev, cap));
+    slot->cap = cap;
+  }
+  memcpy(slot->host, img, bytes);
+  *slot_ack(slot) = 0;
+  B200MT_CUDA(cudaMemcpyAsync(slot->dev, slot->host, bytes, cudaMemcpyHostToDevice, stream));
+  B200MT_CUDA(cudaMemcpyAsync(const_cast<uint32_t*>(slot_ack(slot)), slot->dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+  B200MT_CUDA(cudaEventRecord(slot->uploaded, stream));
+  slot->hash = hash; slot->bytes = bytes; slot->valid = true;
+  slot->users.push_back(stream);
+  g_uploads.fetch_add(1, std::memory_order_relaxed);
+  return 0;
+}
+
+void fill_view(const Slot* slot, const ImageLayout& lay, int T, const Tiling& tiling, TableView* out) {
+  out->ptrs = reinterpret_cast<const unsigned long long*>(slot->dev + lay.off_ptrs);
+  out->numel = reinterpret_cast<const long long*>(slot->dev + lay.off_numel);
+  out->tile_prefix = reinterpret_cast<const int*>(slot->dev + lay.off_prefix);
+  out->ntensors = T;
+  out->ntiles = (int)lay.ntiles;
+  out->tile_elems = tiling.tile_elems;
+  out->ppc = tiling.ppc;
+  out->chunk_elems = tiling.chunk_elems;
+}
+
+inline void note_reader(Slot* slot, cudaStream_t stream) {
+  for (cudaStream_t u : slot->readers) if (u == stream) return;
+  slot->readers.push_back(stream);
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// prepared list sets (b200mt_lists_prepare): caller-owned resident tables, no per-call image / hash / compare
+// ---------------------------------------------------------------------------------------------
+}  // namespace b200mt
+
+struct b200mt_prepared {
+  uint32_t magic = 0;
+  int device = 0, depth = 0, ntensors = 0;
+  std::vector<const void*> ptrs;
+  std::vector<int64_t> numel;
+  struct Entry { b200mt::Tiling tiling; b200mt::ImageLayout lay; b200mt::Slot slot; };
+  std::vector<Entry*> entries;    // one resident table per tiling the handle has been used with (element-wise, norm ...)
+};
+
+namespace b200mt {
+
+constexpr uint32_t kPreparedMagic = 0xb2009e9aU;
+
+static int acquire_prepared(const b200mt_lists* L, const Tiling& tiling, cudaStream_t stream, TableView* out) {
+  b200mt_prepared* h = const_cast<b200mt_prepared*>(reinterpret_cast<const b200mt_prepared*>(L->prepared));
+  B200MT_CHECK(h->magic == kPreparedMagic, "lists->prepared is not a live handle of b200mt_lists_prepare");
+  B200MT_CHECK(h->device == L->device && h->depth == L->depth && h->ntensors == L->ntensors,
+               "lists->prepared was made for another list set (device %d depth %d tensors %d, now %d %d %d)", h->device, h->depth,
+               h->ntensors, L->device, L->depth, L->ntensors);
+  DevCtx* ctx = ctx_for_current_device(L->device);
+  bool capturing = false;
+  if (stream_is_capturing(stream, &capturing)) return 1;
+  b200mt_prepared::Entry* e = nullptr;
+  for (b200mt_prepared::Entry* c : h->entries)
+    if (c->tiling.tile_elems == tiling.tile_elems && c->tiling.ppc == tiling.ppc && c->tiling.chunk_elems == tiling.chunk_elems) { e = c; break; }
+  if (e) {
+    g_hits.fetch_add(1, std::memory_order_relaxed);
+    if (attach_stream(&e->slot, stream, capturing)) return 1;
+  } else {
+    B200MT_CHECK(!capturing, "stream capture: this prepared list set has not been used with this kind of op before the capture "
+                             "began; run the captured calls once (warm-up) first");
+    e = new b200mt_prepared::Entry();
+    e->tiling = tiling;
+    char* img = nullptr;
+    if (build_image(h->ptrs.data(), h->numel.data(), h->depth, h->ntensors, tiling, &e->lay, &img) ||
+        upload_slot(ctx, &e->slot, img, e->lay.bytes, 0, stream)) {
+      delete e;
+      return 1;
+    }
+    h->entries.push_back(e);
+  }
+  fill_view(&e->slot, e->lay, h->ntensors, tiling, out);
+  return 0;
+}
+
+int acquire_table(const b200mt_lists* L, int dmin, int dmax, const Tiling& tiling,
+                  cudaStream_t stream, TableView* out) {
+  B200MT_CHECK(L->depth >= dmin && L->depth <= dmax, "tensor_lists.size() != depth");
+  if (L->prepared) return acquire_prepared(L, tiling, stream, out);
+  const int T = L->ntensors, D = L->depth;
+  DevCtx* ctx = ctx_for_current_device(L->device);
+
+  // ---- build the image in host staging memory
+  ImageLayout lay;
+  char* img = nullptr;
+  if (build_image(L->ptrs, L->numel, D, T, tiling, &lay, &img)) return 1;
+  const size_t bytes = lay.bytes;
   const uint64_t hash = hash_words(img, bytes);
 
   // ---- look it up
@@ -234,20 +400,7 @@ int acquire_table(const b200mt_lists* L, int dmin, int dmax, const Tiling& tilin
   if (stream_is_capturing(stream, &capturing)) return 1;
   if (slot) {
     g_hits.fetch_add(1, std::memory_order_relaxed);
-    // the upload is followed by a 4-byte copy of the table's magic word back into pinned memory: seeing it there
-    // proves the upload is over without any CUDA call (none that queries or waits is safe while capturing)
-    if (!slot->upload_done && *slot_ack(slot) == kMagic) slot->upload_done = true;
-    bool known = false;
-    for (cudaStream_t u : slot->users) known = known || (u == stream);
-    if (!known) {  // first use on this stream: order after the upload, unless it is known to be over
-      if (!slot->upload_done) {
-        B200MT_CHECK(!capturing, "stream capture: the upload of this tensor list's descriptor table is still in flight on "
-                                 "another stream; synchronise before capturing");
-        B200MT_CUDA(cudaStreamWaitEvent(stream, slot->uploaded, 0));
-      }
-      slot->users.push_back(stream);
-    }
-    if (capturing) slot->pinned = true;
+    if (attach_stream(slot, stream, capturing)) return 1;
   } else {
     B200MT_CHECK(!capturing, "stream capture: this tensor list has not been seen before the capture began; run the "
                              "captured calls once (warm-up) with the same tensors first");
@@ -260,50 +413,21 @@ int acquire_table(const b200mt_lists* L, int dmin, int dmax, const Tiling& tilin
     }
     B200MT_CHECK(slot != nullptr, "all %d descriptor-table slots of device %d are held by captured CUDA graphs", kSlots, L->device);
     if (!ctx->tmp_ev) B200MT_CUDA(cudaEventCreateWithFlags(&ctx->tmp_ev, cudaEventDisableTiming));
-    if (!slot->uploaded) B200MT_CUDA(cudaEventCreateWithFlags(&slot->uploaded, cudaEventDisableTiming));
     if (slot->valid) {
       // (a) the pinned shadow may still be the source of an in-flight upload
-      B200MT_CUDA(cudaEventSynchronize(slot->uploaded));
+      if (slot->uploaded) B200MT_CUDA(cudaEventSynchronize(slot->uploaded));
       // (b) kernels on other streams may still read the device copy: order this stream after them
-      for (cudaStream_t u : slot->users) {
+      for (cudaStream_t u : slot->readers) {
         if (u == stream) continue;
         B200MT_CUDA(cudaEventRecord(ctx->tmp_ev, u));
         B200MT_CUDA(cudaStreamWaitEvent(stream, ctx->tmp_ev, 0));
       }
     }
-    slot->valid = false;
-    slot->upload_done = false;
-    slot->users.clear();
-    if (slot->cap < bytes + kAckBytes) {
-      // Growing: the old device buffer may be read by kernels on this stream -> retire, don't free.
-      if (slot->dev) ctx->retired.push_back(slot->dev);
-      if (slot->host) cudaFreeHost(slot->host);
-      slot->host = slot->dev = nullptr; slot->cap = 0;
-      size_t cap = 16384;
-      while (cap < bytes + kAckBytes) cap *= 2;     // the last kAckBytes of the pinned shadow hold the upload acknowledgement
-      B200MT_CUDA(cudaHostAlloc((void**)&slot->host, cap, cudaHostAllocDefault));
-      B200MT_CUDA(cudaMalloc((void**)&slot->dev, cap));
-      slot->cap = cap;
-    }
-    memcpy(slot->host, img, bytes);
-    *slot_ack(slot) = 0;
-    B200MT_CUDA(cudaMemcpyAsync(slot->dev, slot->host, bytes, cudaMemcpyHostToDevice, stream));
-    B200MT_CUDA(cudaMemcpyAsync(const_cast<uint32_t*>(slot_ack(slot)), slot->dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
-    B200MT_CUDA(cudaEventRecord(slot->uploaded, stream));
-    slot->hash = hash; slot->bytes = bytes; slot->valid = true;
-    slot->users.push_back(stream);
-    g_uploads.fetch_add(1, std::memory_order_relaxed);
+    if (upload_slot(ctx, slot, img, bytes, hash, stream)) return 1;
   }
+  note_reader(slot, stream);
   slot->tick = ++ctx->tick;
-
-  out->ptrs = reinterpret_cast<const unsigned long long*>(slot->dev + off_ptrs);
-  out->numel = reinterpret_cast<const long long*>(slot->dev + off_numel);
-  out->tile_prefix = reinterpret_cast<const int*>(slot->dev + off_prefix);
-  out->ntensors = T;
-  out->ntiles = (int)acc;
-  out->tile_elems = tiling.tile_elems;
-  out->ppc = tiling.ppc;
-  out->chunk_elems = tiling.chunk_elems;
+  fill_view(slot, lay, T, tiling, out);
   return 0;
 }
 
@@ -351,10 +475,75 @@ int acquire_scratch(cudaStream_t stream, size_t bytes, void** out) {
 using namespace b200mt;
 
 extern "C" const char* b200mt_last_error(void) { return g_err.c_str(); }
-extern "C" int b200mt_version(void) { return 100; }
+extern "C" int b200mt_version(void) { return 101; }
 extern "C" int64_t b200mt_launch_count(void) { return g_launches.load(); }
 extern "C" int64_t b200mt_table_uploads(void) { return g_uploads.load(); }
 extern "C" int64_t b200mt_table_hits(void) { return g_hits.load(); }
+
+extern "C" int b200mt_lists_prepare(const b200mt_lists* L, b200mt_prepared** out) {
+  B200MT_CHECK(out != nullptr, "b200mt_lists_prepare: out is NULL");
+  *out = nullptr;
+  if (check_common(L, 1)) return 1;
+  B200MT_CHECK(L->prepared == nullptr, "b200mt_lists_prepare: lists->prepared must be NULL");
+  for (int t = 0; t < L->ntensors; t++) B200MT_CHECK(L->numel[t] >= 0, "negative numel for tensor %d", t);
+  b200mt_prepared* h = new b200mt_prepared();
+  h->magic = kPreparedMagic;
+  h->device = L->device; h->depth = L->depth; h->ntensors = L->ntensors;
+  h->ptrs.assign(L->ptrs, L->ptrs + (size_t)L->depth * L->ntensors);
+  h->numel.assign(L->numel, L->numel + L->ntensors);
+  *out = h;
+  return 0;
+}
+
+extern "C" int b200mt_lists_release(b200mt_prepared* h) {
+  if (!h) return 0;
+  B200MT_CHECK(h->magic == kPreparedMagic, "b200mt_lists_release: not a live handle");
+  CallGuard guard(h->device);
+  if (guard.status) return 1;
+  h->magic = 0;
+  for (b200mt_prepared::Entry* e : h->entries) {
+    // kernels in flight may still read the table: cudaFree waits for the device, which a release may afford
+    if (e->slot.uploaded) { cudaEventSynchronize(e->slot.uploaded); cudaEventDestroy(e->slot.uploaded); }
+    if (e->slot.dev) cudaFree(e->slot.dev);
+    if (e->slot.host) cudaFreeHost(e->slot.host);
+    delete e;
+  }
+  delete h;
+  return 0;
+}
+
+extern "C" int b200mt_trace_begin(int max_launches) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  B200MT_CHECK(max_launches > 0 && max_launches <= 65536, "b200mt_trace_begin: max_launches must be in 1..65536");
+  B200MT_CHECK(!g_tracing.load(), "b200mt_trace_begin: a trace is already running");
+  while ((int)g_trace.size() < max_launches) {
+    TraceRec r;
+    B200MT_CUDA(cudaEventCreate(&r.a));
+    B200MT_CUDA(cudaEventCreate(&r.b));
+    g_trace.push_back(r);
+  }
+  g_trace_used = 0;
+  g_tracing.store(true);
+  return 0;
+}
+
+extern "C" int b200mt_trace_end(float* ms, int capacity, int* count) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  B200MT_CHECK(g_tracing.load(), "b200mt_trace_end: no trace is running");
+  g_tracing.store(false);
+  const int n = (int)g_trace_used;
+  if (count) *count = n;
+  for (int i = 0; i < n && i < capacity; i++) {
+    B200MT_CUDA(cudaEventSynchronize(g_trace[i].b));
+    B200MT_CUDA(cudaEventElapsedTime(&ms[i], g_trace[i].a, g_trace[i].b));
+  }
+  return 0;
+}
+
+extern "C" const char* b200mt_trace_name(int i) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  return (i >= 0 && i < (int)g_trace_used) ? g_trace[i].name.c_str() : "";
+}
 
 extern "C" int b200mt_set_tuning(int tile_elems, int grid_cap) {
   std::lock_guard<std::recursive_mutex> lk(g_mu);

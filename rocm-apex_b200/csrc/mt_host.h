@@ -6,6 +6,7 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <string>
+#include <typeinfo>
 
 #include "../../include/b200mt.h"
 #include "mt_device.cuh"
@@ -64,13 +65,22 @@ int acquire_table(const b200mt_lists* L, int expect_depth_min, int expect_depth_
 // zero (they hold self-resetting completion counters).
 int acquire_scratch(cudaStream_t stream, size_t bytes, void** out);
 
+// ---- launch trace (b200mt_trace_begin / _end): when on, every kernel launch of the library is bracketed by a pair
+// of CUDA events on its stream, so a caller can read per-kernel durations of a multi-kernel entry point live
+// (bench.py uses it for the roofline of the dominant kernel).  Off by default: one predictable branch per launch.
+bool trace_on();
+void trace_before(cudaStream_t stream, const char* mangled_name);
+void trace_after(cudaStream_t stream);
+
 int grid_for(int ntiles);
 bool pdl_enabled();   // env B200MT_PDL (default on): launch streaming kernels with programmatic stream serialization
 
 template <class Op>
 int launch_stream(const TableView& tv, const Op& op, cudaStream_t stream, bool allow_pdl = true) {
   if (tv.ntiles <= 0) return 0;
-  if (allow_pdl && pdl_enabled()) {
+  const bool tracing = trace_on();
+  if (tracing) trace_before(stream, typeid(Op).name());
+  if (allow_pdl && pdl_enabled() && !tracing) {   // traced launches run serialised: the events must see the whole kernel
     // Programmatic dependent launch: this grid may become resident while the previous kernel of the
     // stream drains its last wave; it touches nothing that kernel produced before griddepcontrol.wait.
     cudaLaunchConfig_t cfg = {};
@@ -87,6 +97,7 @@ int launch_stream(const TableView& tv, const Op& op, cudaStream_t stream, bool a
   } else {
     mt_stream_kernel<Op><<<grid_for(tv.ntiles), Op::THREADS, 0, stream>>>(tv, op);
   }
+  if (tracing) trace_after(stream);
   count_launch();
   B200MT_CUDA(cudaGetLastError());
   return 0;

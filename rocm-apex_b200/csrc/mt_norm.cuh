@@ -62,6 +62,10 @@ static __global__ void __launch_bounds__(kCleanupThreads) norm_cleanup_kernel(co
   __shared__ float red[kCleanupThreads / 32];
   __shared__ int s_last;
   const int tid = threadIdx.x;
+  // launched with programmatic stream serialization: this grid may become resident while pass 1 drains its last wave;
+  // everything it reads (partials, the flag) is produced by pass 1, so wait for that kernel to complete and flush first
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   const bool skip = a.gated && (*reinterpret_cast<volatile int*>(a.noop) != 0);
   bool bad = false;
 
@@ -138,7 +142,23 @@ inline int launch_norm_cleanup(const TableView& tv, const NormScratch& s, int ns
   a.ret[0] = ret0; a.ret[1] = ret1;
   a.ret_per_tensor[0] = per0; a.ret_per_tensor[1] = per1;
   int grid = tv.ntensors < 2048 ? tv.ntensors : 2048;
-  norm_cleanup_kernel<<<grid, kCleanupThreads, 0, stream>>>(a);
+  const bool tracing = trace_on();
+  if (tracing) trace_before(stream, "norm_cleanup_kernel");
+  if (pdl_enabled() && !tracing) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kCleanupThreads);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    B200MT_CUDA(cudaLaunchKernelEx(&cfg, norm_cleanup_kernel, a));
+  } else {
+    norm_cleanup_kernel<<<grid, kCleanupThreads, 0, stream>>>(a);
+  }
+  if (tracing) trace_after(stream);
   count_launch();
   B200MT_CUDA(cudaGetLastError());
   return 0;

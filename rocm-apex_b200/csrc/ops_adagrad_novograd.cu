@@ -143,6 +143,7 @@ extern "C" int b200mt_novograd(const b200mt_lists* L, int chunk_size, int32_t* n
 
   // ---- 1. grad_norms <- blend(grad_norms, per-tensor norm of g): a one-list pass over g + second pass
   b200mt_lists G = *L;
+  G.prepared = nullptr;   // a handle describes the whole 3-list set; this one-list view goes through the table cache
   G.depth = 1;   // list 0 (g) only: list-major layout means its pointers are the first ntensors entries
   const int tile_scale = (L->dtype[0] == B200MT_F16 || L->dtype[0] == B200MT_BF16) ? 2 : 1;
   TableView tg;

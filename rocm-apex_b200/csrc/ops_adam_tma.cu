@@ -138,16 +138,20 @@ int adam_tma_launch(const TableView& tv, float beta1, float beta2, float bc1, fl
   if (tv.ntiles <= 0) return 0;
   const size_t smem = (size_t)4 * tv.tile_elems * sizeof(float);
   B200MT_CHECK(smem <= 200 * 1024 && tv.tile_elems % 4 == 0, "adam (bulk-copy path): unsupported tile of %d elements", tv.tile_elems);
-  static size_t configured = 0;
-  if (configured < smem) {
+  // the opt-in for more than 48 KB of dynamic shared memory is a per-DEVICE attribute of the kernel
+  static size_t configured[64] = {0};
+  int device = 0;
+  B200MT_CUDA(cudaGetDevice(&device));
+  B200MT_CHECK(device >= 0 && device < 64, "invalid device ordinal %d", device);
+  if (configured[device] < smem) {
     B200MT_CUDA(cudaFuncSetAttribute(adam_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
+    configured[device] = smem;
   }
   AdamTmaParams a;
   a.beta1 = beta1; a.beta2 = beta2; a.bc1 = bc1; a.bc2 = bc2; a.eps = eps; a.lr = lr; a.decay = decay;
   a.grad_scale = grad_scale; a.mode = mode;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)tv.ntiles);
+  cfg.gridDim = dim3((unsigned)tv.ntiles);   // one tile per CTA by construction: B200MT_GRID_CAP does not apply to this path
   cfg.blockDim = dim3(256);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;

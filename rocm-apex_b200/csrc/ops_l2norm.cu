@@ -14,12 +14,19 @@ namespace b200mt {
 #ifndef B200MT_NORM16_UNROLL
 #define B200MT_NORM16_UNROLL 1   // swept 1/2/4/8 on 4x256M fp16: 312 / 325 / 394 / 552 us (profiles/sweep_norm2_r01.txt)
 #endif
+#ifndef B200MT_NORM32_UNROLL
+#define B200MT_NORM32_UNROLL 4
+#endif
+#ifndef B200MT_NORM32_VEC
+#define B200MT_NORM32_VEC 4
+#endif
 template <typename Tx>
 struct L2NormOp : OpBase {
   using Types = TypeList<Tx>;
   static constexpr unsigned STORES = 0;
-  static constexpr int VEC = (Elem<Tx>::SIZE == 2) ? B200MT_NORM16_VEC : 4;
-  static constexpr int UNROLL = (Elem<Tx>::SIZE == 2) ? B200MT_NORM16_UNROLL : 4;
+  static constexpr int MIN_CTAS = (Elem<Tx>::SIZE == 2) ? B200MT_NORM16_MIN_CTAS : B200MT_NORM32_MIN_CTAS;
+  static constexpr int VEC = (Elem<Tx>::SIZE == 2) ? B200MT_NORM16_VEC : B200MT_NORM32_VEC;
+  static constexpr int UNROLL = (Elem<Tx>::SIZE == 2) ? B200MT_NORM16_UNROLL : B200MT_NORM32_UNROLL;
   static constexpr int THREADS = 256;
   struct State { float acc = 0.f; };
   float* partials;
@@ -44,6 +51,7 @@ template <typename Tin, typename Tout>
 struct L2NormScaleOp : OpBase {
   using Types = TypeList<Tin, Tout>;
   static constexpr unsigned STORES = 0b10;
+  static constexpr int MIN_CTAS = B200MT_NORM32_MIN_CTAS;
   static constexpr bool ANY16 = Elem<Tin>::SIZE == 2 || Elem<Tout>::SIZE == 2;   // as for ScaleOp
   static constexpr int UNROLL = ANY16 ? 2 : 4;
   static constexpr int VEC = ANY16 ? 8 : 4;

@@ -14,16 +14,25 @@
 //  * the array is B200MT_NOALLOC_SCRATCH_BYTES (about 257 KiB) of device memory on EVERY GPU that
 //    loads this library, from load until the process exits, whether or not this function is called;
 //  * inputs needing more than B200MT_NOALLOC_MAX_TILES (65536) scheduling tiles are refused with an
-//    error -- tiles are 16384 elements here whatever B200MT_NORM_TILE_ELEMS says, so with
-//    chunk_size >= 16384 that is 1,073,741,824 elements; small chunk sizes lower it (one tile per
-//    chunk at least);
+//    error.  The limit is in TILES, not elements: a chunk of chunk_size elements is cut into
+//    ppc = ceil(chunk_size / 16384) equal tiles (16384 whatever B200MT_NORM_TILE_ELEMS says), so an
+//    input of numel elements needs floor(numel / chunk_size) * ppc tiles plus those of the last,
+//    partial chunk.  That is 65536 * 16384 = 1,073,741,824 elements only when chunk_size is a
+//    multiple of 16384 (65536, the default, is); chunk_size 16400 gives 2 tiles of 8208 per chunk
+//    and a limit of 32768 chunks = 537,395,200 elements, chunk_size 20000 about 655 M, and any
+//    chunk_size below 16384 gives one tile per chunk, i.e. 65536 * chunk_size elements.  Size your
+//    buffer from that formula (or from a trial call: the refusal is decided on the host, before
+//    anything is launched);
 //  * all calls on a device share the array and it keeps whatever the previous call left in it.  The
 //    function re-initialises the few words that must start at zero itself, at the head of its own
 //    work on the stream, so back-to-back calls on one stream are fine; two calls whose GPU work can
 //    overlap (different streams with no ordering between them, or two host threads on different
 //    streams) race on the array and give garbage.  Order them yourself;
 //  * the first call on each device looks up the array's device address (a host-side query, no
-//    allocation).  Make that first call before you begin any stream capture on that device.
+//    allocation) and keeps it for the life of the process.  Make that first call before you begin
+//    any stream capture on that device.  The kept address does not survive cudaDeviceReset() or the
+//    destruction of the device's primary context: a host that tears contexts down must not call
+//    this entry point afterwards.
 #include "mt_dispatch.h"
 #include "mt_norm.cuh"
 

@@ -11,6 +11,17 @@
 #ifndef B200MT_SCALE_UNROLL
 #define B200MT_SCALE_UNROLL 2
 #endif
+// fp32-only lists: vector width and vectors in flight per thread (swept with the occupancy, profiles/sweep_light_r02.txt)
+// one 256-bit access per thread at 8 CTAs/SM: equal to 4 x 128-bit on large lists, 3 % faster on the ResNet-50 step
+#ifndef B200MT_SCALE32_VEC
+#define B200MT_SCALE32_VEC 8
+#endif
+#ifndef B200MT_SCALE32_UNROLL
+#define B200MT_SCALE32_UNROLL 1
+#endif
+#ifndef B200MT_AXPBY_UNROLL
+#define B200MT_AXPBY_UNROLL 2
+#endif
 
 namespace b200mt {
 
@@ -24,11 +35,12 @@ template <typename Tin, typename Tout>
 struct ScaleOp : OpBase {
   using Types = TypeList<Tin, Tout>;
   static constexpr unsigned STORES = 0b10;
+  static constexpr int MIN_CTAS = B200MT_SCALE_MIN_CTAS;
   // a 16-bit list wants 8 elements (one 128-bit access) per vector; fp32-only lists are as fast or
   // faster (small tensor lists) with 4 x 4
   static constexpr bool ANY16 = Elem<Tin>::SIZE == 2 || Elem<Tout>::SIZE == 2;
-  static constexpr int UNROLL = ANY16 ? B200MT_SCALE_UNROLL : 4;
-  static constexpr int VEC = ANY16 ? B200MT_SCALE_VEC : 4;
+  static constexpr int UNROLL = ANY16 ? B200MT_SCALE_UNROLL : B200MT_SCALE32_UNROLL;
+  static constexpr int VEC = ANY16 ? B200MT_SCALE_VEC : B200MT_SCALE32_VEC;
   struct State { bool bad = false; };
   float scale;
   int* noop;
@@ -48,7 +60,8 @@ template <typename Tx, typename Ty, typename Tout>
 struct AxpbyOp : OpBase {
   using Types = TypeList<Tx, Ty, Tout>;
   static constexpr unsigned STORES = 0b100;
-  static constexpr int UNROLL = 2;
+  static constexpr int MIN_CTAS = B200MT_SCALE_MIN_CTAS;
+  static constexpr int UNROLL = B200MT_AXPBY_UNROLL;
   struct State { bool bad = false; };
   float a, b;
   int arg_to_check;

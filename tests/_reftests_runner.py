@@ -1,0 +1,57 @@
+"""Subprocess body of tests/test_reference_suite_gpu.py: runs the REFERENCE's own unit tests for the hot path
+(/root/reference/tests/L0/run_amp and run_optimizers, staged unmodified under oracle/_ref/pyref_tests by
+oracle/build_ref.sh) with the reference's own Python package (oracle/_ref/pyref) over one of two back ends:
+
+  python tests/_reftests_runner.py ours <out.json> <dir/test_file.py> ...   amp_C = this repo's shim over libb200mt.so
+  python tests/_reftests_runner.py ref  <out.json> <dir/test_file.py> ...   amp_C = the reference's kernels (amp_C_ref.so)
+
+Writes {test id: "ok" | "fail: ..." | "error: ..." | "skip: ..."} as JSON.
+"""
+import json
+import os
+import sys
+import unittest
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from _refpy_worker import ROOT, setup   # noqa: E402
+
+TESTS = os.path.join(ROOT, "oracle", "_ref", "pyref_tests")
+
+
+class Result(unittest.TextTestResult):
+    def __init__(self, *a, **k):
+        super().__init__(*a, **k)
+        self.outcomes = {}
+
+    def addSuccess(self, test):
+        super().addSuccess(test); self.outcomes[test.id()] = "ok"
+
+    def addFailure(self, test, err):
+        super().addFailure(test, err); self.outcomes[test.id()] = "fail: " + self._exc_info_to_string(err, test)[-1500:]
+
+    def addError(self, test, err):
+        super().addError(test, err); self.outcomes[test.id()] = "error: " + self._exc_info_to_string(err, test)[-1500:]
+
+    def addSkip(self, test, reason):
+        super().addSkip(test, reason); self.outcomes[test.id()] = "skip: " + reason
+
+
+def main():
+    backend, out, files = sys.argv[1], sys.argv[2], sys.argv[3:]
+    setup(backend)
+    outcomes = {}
+    for rel in files:
+        d, f = os.path.split(rel)
+        sys.path.insert(0, os.path.join(TESTS, d))          # the tests do `from utils import common_init`
+        suite = unittest.defaultTestLoader.discover(os.path.join(TESTS, d), pattern=f, top_level_dir=os.path.join(TESTS, d))
+        runner = unittest.TextTestRunner(resultclass=Result, verbosity=1, stream=sys.stderr)
+        r = runner.run(suite)
+        outcomes.update(r.outcomes)
+        sys.path.pop(0)
+    with open(out, "w") as fh:
+        json.dump(outcomes, fh, indent=1)
+    print("reference tests over %s: %d ok of %d" % (backend, sum(v == "ok" for v in outcomes.values()), len(outcomes)))
+
+
+if __name__ == "__main__":
+    main()

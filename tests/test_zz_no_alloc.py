@@ -49,6 +49,12 @@ def test_noalloc_norm_matches_regular_entry_point_twice_in_a_row(dtype):
         assert int(f0) == int(f1) == 0
         assert abs(float(got) - float(want)) <= RTOL * abs(float(want)), (float(got), float(want))
         assert abs(float(got) - float(x.float().norm())) <= 1e-4 * float(x.float().norm())
+        # and against the reference's own kernel (oracle/_ref/amp_C_ref.so), when it was built
+        from util import load_ref
+        refm = load_ref("amp_C_ref")
+        if refm is not None:
+            rn, _ = refm.multi_tensor_l2norm(CHUNK, torch.zeros(1, dtype=torch.int32, device="cuda"), [[x]], False)
+            assert abs(float(got) - float(rn)) <= RTOL * abs(float(rn)), (float(got), float(rn))
 
 
 def test_noalloc_flag_and_reuse_after_overflow():
@@ -81,3 +87,22 @@ def test_noalloc_rejects_inputs_beyond_the_fixed_scratch():
     assert rc != 0
     msg = mt.lib.b200mt_last_error().decode()
     assert "fixed scratch holds 65536" in msg and "70000 tiles" in msg
+
+
+def test_noalloc_limit_at_a_chunk_size_that_is_not_a_multiple_of_the_tile():
+    """chunk_size 16400 is cut into 2 tiles of 8208: the limit is 32768 chunks = 537,395,200 elements, not the
+    1,073,741,824 of chunk sizes that are multiples of 16384.  Exactly at the limit the call works; one element more
+    is refused on the host."""
+    import _b200mt as mt
+    chunk = 16400
+    n = 32768 * chunk
+    x = torch.ones(n + 1, dtype=torch.float16, device="cuda")
+    f = torch.zeros(1, dtype=torch.int32, device="cuda")
+    got = _noalloc(mt, x[:n], chunk, f)
+    want = float(n) ** 0.5
+    assert int(f) == 0 and abs(float(got) - want) <= RTOL * want, (float(got), want)
+    ret = torch.empty(1, device="cuda")
+    rc = mt.lib.b200mt_l2norm_flat_noalloc(x.data_ptr(), mt.F16, n + 1, chunk, f.data_ptr(), ret.data_ptr(), 0, mt.stream_ptr(0))
+    assert rc != 0
+    msg = mt.lib.b200mt_last_error().decode()
+    assert "65537 tiles" in msg and "tile 8208 elements" in msg, msg
