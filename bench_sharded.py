@@ -20,7 +20,7 @@ NVLINK_GBS = 770.0     # measured peer-copy bandwidth per direction (B200_PROFIL
 
 
 def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, stream, flat, nparams, shapes, model_name, lib,
-                  parity=None, parity_ok=True):
+                  parity=None, parity_ok=True, nvlink_measured=None):
     from bench import peaks, pinned_near_gpu, gpu_numa_cpus, METRIC, UNIT
     clocks = sampler.stop() if rank == 0 else None
     host = pinned_near_gpu(1 << 27, torch.bfloat16, local)
@@ -71,7 +71,11 @@ def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, str
                        "e5m2_allgather": bool(opt._e5m2),
                        "l2": "inputs larger than L2 (%.1f GB of optimizer state per rank)" % (12.0 * shard_elems / 1e9)},
             "roofline": {"bound": "nvlink", "achieved": nv_bytes / (ms * 1e-3) / 1e9, "peak": NVLINK_GBS, "unit": "GB/s",
-                         "frac": nv_bytes / (ms * 1e-3) / 1e9 / NVLINK_GBS, "traffic": None,
+                         "frac": nv_bytes / (ms * 1e-3) / 1e9 / NVLINK_GBS,
+                         "traffic": (nvlink_measured or {}).get("tx_bytes_per_step_per_gpu"),
+                         "traffic_source": "NVLink bytes this GPU transmitted per step (NVML link counters around the timed loop), "
+                                           "the counterpart of `bytes_per_launch` for an NVLink-bound kernel",
+                         "nvlink_measured": nvlink_measured,
                          "kernel": "mt_stream_kernel<DistAdamOp<mc_bf16,true>> (includes both barriers)",
                          "bytes_per_launch": nv_bytes, "avg_launch_ms": ms,
                          "peak_source": "measured peer-copy bandwidth per direction (B200_PROFILING.md), 900 nominal",
@@ -201,8 +205,12 @@ def run_sharded(args):
     stream = torch.cuda.current_stream(dev)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = lib.b200mt_launch_count()
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    from nvlink_counters import NvlinkCounters
+    nvl = NvlinkCounters(local)
     torch.cuda.synchronize()
     dist.barrier()
+    nv0 = nvl.read() if nvl.ok else None
     e0.record(stream)
     for _ in range(args.steps):
         step()
@@ -210,13 +218,25 @@ def run_sharded(args):
     torch.cuda.synchronize()
     dist.barrier()
     ms = e0.elapsed_time(e1) / args.steps
+    # bytes this GPU's NVLinks carried per step, from the driver's counters (max over ranks below)
+    nv_tx, nv_rx = ([d / args.steps for d in nvl.delta(nv0)] if nvl.ok else (None, None))
+    tnv = torch.tensor([nv_tx or 0.0, nv_rx or 0.0, 1.0 if nvl.ok else 0.0], device=dev, dtype=torch.float64)
+    dist.all_reduce(tnv, op=dist.ReduceOp.MAX)
+    nvlink_measured = None
+    if float(tnv[2]) > 0:
+        nvlink_measured = {"tx_bytes_per_step_per_gpu": float(tnv[0]), "rx_bytes_per_step_per_gpu": float(tnv[1]),
+                           "tx_gbs": float(tnv[0]) / (ms * 1e-3) / 1e9, "rx_gbs": float(tnv[1]) / (ms * 1e-3) / 1e9,
+                           "source": "NVML NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX/RX summed over the GPU's links, read around the "
+                                     "timed loop; max over ranks"}
+    else:
+        nvlink_measured = {"unavailable": nvl.err}
     launches = lib.b200mt_launch_count() - launches0
     clocks = sampler.stop() if rank == 0 else None
 
     shard_elems = opt._layout["shard"] * K
     if fused:
         return _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, stream, flat, nparams, shapes, model_name, lib,
-                             parity, parity_ok)
+                             parity, parity_ok, nvlink_measured)
     # shard kernel alone (no collectives): the roofline of the dominant kernel on this rank
     ks = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     kreps = 5
@@ -298,7 +318,7 @@ def run_sharded(args):
                        "peak_gbs": NVLINK_GBS, "frac_rs": nv_bytes / (rs_ms * 1e-3) / 1e9 / NVLINK_GBS,
                        "frac_ag": ag_bytes / (ag_ms * 1e-3) / 1e9 / NVLINK_GBS,
                        "step_floor_ms": (nv_bytes + ag_bytes) / (NVLINK_GBS * 1e9) * 1e3, "e5m2_allgather": bool(opt._e5m2),
-                       "overlap_efficiency": (rs_ms + ag_ms) / ms, "shard_kernel_ms": kernel_ms},
+                       "overlap_efficiency": (rs_ms + ag_ms) / ms, "shard_kernel_ms": kernel_ms, "measured": nvlink_measured},
             "cpu_baseline": None,
             "e2e": {"value": nparams / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 2 * total * world, "d2h_bytes_per_step": 2 * world,
                     "ms_per_step": e2e_ms, "steps": e2e_steps, "pinned_on_gpu_numa_node": numa_known,

@@ -195,6 +195,10 @@ int b200mt_dist_lamb_stage2(const b200mt_lists* lists, int chunk_size, int32_t* 
  * parameter broadcast (half the bytes through the switch).  Every fragment must be a multiple of 8
  * elements; lists 0-2 32-byte, list 3 16-byte, list 4 16-byte (8-byte when e5m2) aligned.  The caller brackets the launch with cross-GPU
  * barriers (all ranks' gradients written before; all ranks' kernels finished after). */
+/* measurement switches, OR-ed into `mode`: the named list holds ordinary device addresses, so the kernel keeps only one
+ * of its two collectives (tools/nvls_probe.py times the three forms) */
+#define B200MT_NVLS_LOCAL_GRADS 0x100
+#define B200MT_NVLS_LOCAL_COPY  0x200
 int b200mt_dist_adam_nvls(const b200mt_lists* lists, int chunk_size, int32_t* noop,
                           const float* per_tensor_beta1, const float* per_tensor_beta2,
                           const int32_t* per_tensor_bias_correction, const float* per_tensor_eps,

@@ -1,7 +1,9 @@
 """TEST INFRASTRUCTURE ONLY -- CPU restatement of the sharded LAMB kernels of DistributedFusedLAMB
-(apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb_kernel.cu).  Parity for these two kernels is anchored
-on this restatement and on the unsharded LAMB (the reference's kernel file does not compile against torch 2.11,
-`:352` ambiguous operator!=, so there is no oracle/_ref build of it): "parity unpinned" against the reference binary.
+(apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb_kernel.cu).  Pinned against the reference's own kernels:
+oracle/build_ref.sh compiles that file unmodified for sm_100a (with the -D__CUDA_NO_HALF*_ defines torch's CUDAExtension
+adds, without which :352 meets an ambiguous operator!=) into oracle/_ref/distributed_lamb_cuda_ref.so, and
+tests/test_dist_lamb.py::test_dist_lamb_kernels_match_reference_binary compares this restatement AND the sm_100a kernels
+of csrc/ops_dist_lamb.cu with it on identical inputs.
 """
 import math
 

@@ -110,8 +110,12 @@ try:   # optional native list walker (build_packer.py); the Python walker below 
     from _b200mt_pack import pack_lists as _fast_pack
 except ImportError:
     _fast_pack = None
+try:
+    from _b200mt_pack import check_rows
+except ImportError:
+    check_rows = None
 if os.environ.get("B200MT_PY_PACK"):
-    _fast_pack = None
+    _fast_pack = check_rows = None
 
 
 class trace(object):
@@ -203,13 +207,14 @@ class Prepared(Packed):
             pass
 
 
-def prepare(tensor_lists):
-    """-> Prepared: validate and pack `tensor_lists` once, keep a resident descriptor table for them."""
+def prepare(tensor_lists, keep=True):
+    """-> Prepared: validate and pack `tensor_lists` once, keep a resident descriptor table for them.
+    keep=False: the handle does not hold the tensors; the caller re-validates the addresses (q.ptrs) before every use."""
     p = pack(tensor_lists)
     q = Prepared()
     for name in ("struct", "ptrs", "numel", "device", "ntensors", "depth"):
         setattr(q, name, getattr(p, name))
-    q.keep = [list(l) for l in tensor_lists]          # the tensors stay alive as long as the handle does
+    q.keep = [list(l) for l in tensor_lists] if keep else None   # the tensors stay alive as long as the handle does
     h = ctypes.c_void_p()
     check(lib.b200mt_lists_prepare(q.ref(), ctypes.byref(h)))
     q.handle = h.value

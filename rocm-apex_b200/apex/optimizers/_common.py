@@ -34,6 +34,10 @@ class GroupCache(object):
         self.groups = {}
 
     def clear(self):
+        for c in self.groups.values():
+            for b in c[4]:
+                if b[4].get("prep") is not None:
+                    b[4]["prep"].release()
         self.groups = {}
 
     def buckets(self, opt, gi, group, init_state):
@@ -45,13 +49,72 @@ class GroupCache(object):
                 return out
         return self._slow(opt, gi, group, init_state)
 
+    def launch_sets(self, opt, gi, group, init_state):
+        """What step() hands to the kernel, one entry per parameter dtype: the prepared handle (amp_C.prepare) of the
+        bucket's [grads, params, state0, state1] when every gradient still sits at the address it had when the handle was
+        made -- one C loop checks that, together with the identity of the state tensors -- else the four lists.
+        Gradients re-allocated every iteration usually come back at the same addresses (caching allocator), so the
+        handle survives `zero_grad(set_to_none=True)`; a bucket that keeps moving stops being prepared after three misses."""
+        import _b200mt as mt
+        if mt.check_rows is None:
+            return [list(b) for b in self.buckets(opt, gi, group, init_state)]
+        n0, n1 = self.names
+        c = self.groups.get(gi)
+        if c is not None and c[0] is opt.state and c[1] is group["params"] and c[2] == len(group["params"]) \
+                and all(p.grad is None for p in c[3]):
+            out = []
+            for bucket in c[4]:
+                h = bucket[4]
+                if h.get("prep") is not None:
+                    rc = mt.check_rows(bucket[0], n0, n1, h["prep"].ptrs.ctypes.data, h["code"])
+                    if rc == 0:
+                        h["misses"] = 0
+                        out.append(h["prep"])
+                        continue
+                    if rc == 2:
+                        out = None
+                        break
+                gs = []
+                for p, st, t0, t1 in bucket[0]:
+                    g = p.grad
+                    if g is None or st[n0] is not t0 or st[n1] is not t1:
+                        gs = None
+                        break
+                    gs.append(g)
+                if gs is None:
+                    out = None
+                    break
+                out.append(self._maybe_prepare(bucket, gs))
+            if out is not None:
+                return out
+        self._slow(opt, gi, group, init_state)
+        return [self._maybe_prepare(b, [r[0].grad for r in b[0]]) for b in self.groups[gi][4]]
+
+    @staticmethod
+    def _maybe_prepare(bucket, gs):
+        import _b200mt as mt
+        rows, ps, s0, s1, h = bucket
+        lists = [gs, ps, s0, s1]
+        if h.get("prep") is not None:
+            h["prep"].release()
+            h["prep"] = None
+            h["misses"] = h.get("misses", 0) + 1
+        if h.get("misses", 0) >= 3 or any(g.is_sparse for g in gs):
+            return lists
+        try:
+            h["prep"] = mt.prepare(lists, keep=False)      # the gradients are not held: their addresses are re-checked
+            h["code"] = mt.dtype_code(gs[0])
+            return h["prep"]
+        except RuntimeError:
+            return lists                                   # let the plain call report whatever is wrong with the lists
+
     def _fast(self, c):
         n0, n1 = self.names
         for p in c[3]:                       # parameters that had no gradient when the cache was built
             if p.grad is not None:
                 return None
         out = []
-        for rows, ps, s0, s1 in c[4]:
+        for rows, ps, s0, s1, _ in c[4]:
             gs = []
             add = gs.append
             for p, st, t0, t1 in rows:
@@ -83,7 +146,7 @@ class GroupCache(object):
             if not rows:
                 continue
             ps, s0, s1 = [r[0] for r in rows], [r[2] for r in rows], [r[3] for r in rows]
-            cached.append((rows, ps, s0, s1))
+            cached.append((rows, ps, s0, s1, {}))
             out.append(([r[0].grad for r in rows], ps, s0, s1))
         self.groups[gi] = (opt.state, group["params"], len(group["params"]), idle, cached)
         return out

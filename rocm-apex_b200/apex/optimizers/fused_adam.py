@@ -41,8 +41,8 @@ class FusedAdam(torch.optim.Optimizer):
             group["step"] = group.get("step", 0) + 1      # one counter per group, as in the reference
             beta1, beta2 = group["betas"]
             # [g, p, exp_avg, exp_avg_sq] per dtype: the reference's per-parameter loop (:118-160), run once and memoised
-            for lists in self._lists.buckets(self, gi, group, self._init_state):
-                multi_tensor_applier(self.multi_tensor_adam, self._dummy_overflow_buf, list(lists), group["lr"],
+            for lists in self._lists.launch_sets(self, gi, group, self._init_state):
+                multi_tensor_applier(self.multi_tensor_adam, self._dummy_overflow_buf, lists, group["lr"],
                                      beta1, beta2, group["eps"], group["step"], self.adam_w_mode,
                                      1 if group["bias_correction"] else 0, group["weight_decay"])
         return loss

@@ -26,6 +26,7 @@ struct TableView {
   const int*                tile_prefix;  // [ntensors+1] exclusive prefix of tiles per tensor
   int       ntensors;
   int       ntiles;
+  int       nonempty;     // tensors with at least one element
   int       tile_elems;   // elements per scheduling tile
   int       ppc;          // tiles per full chunk (1 for element-wise ops)
   long long chunk_elems;  // chunk length in elements (== tile_elems when ppc == 1)

@@ -17,7 +17,12 @@ namespace b200mt {
 // ---------------------------------------------------------------------------------------------
 static thread_local std::string g_err;
 static std::atomic<int64_t> g_launches{0}, g_uploads{0}, g_hits{0};
-static std::recursive_mutex g_mu;
+static std::recursive_mutex g_mu;           // library-level state: tuning, trace control, shutdown
+// One lock PER DEVICE around a call (table cache, scratch and handles are per device): host threads that drive different
+// GPUs of one process do not serialise on each other.
+static std::recursive_mutex g_dev_mu[64];
+static std::mutex g_trace_mu;               // the trace record list is shared by all devices
+static std::once_flag g_tuning_once;
 static int g_tile_elems = 0;  // 0 = not yet initialised
 static int g_grid_cap = 0;    // 0 = one CTA per tile
 static bool g_pdl = true;     // programmatic dependent launch of the streaming kernels (B200MT_PDL=0 disables)
@@ -49,14 +54,14 @@ const char* dtype_name(int d) {
   }
 }
 
-static void init_tuning() {
-  if (g_tile_elems) return;
+static void init_tuning_once() {
   g_tile_elems = 4096;  // swept on B200 (profiles/sweep_tiles_r01.txt): one CTA per 4096-element tile is fastest
   if (const char* e = getenv("B200MT_TILE_ELEMS")) { int v = atoi(e); if (v >= 64) g_tile_elems = v; }
   if (const char* e = getenv("B200MT_GRID_CAP")) { int v = atoi(e); if (v > 0) g_grid_cap = v; }
   if (const char* e = getenv("B200MT_PDL")) g_pdl = atoi(e) != 0;
   if (const char* e = getenv("B200MT_NORM_TILE_ELEMS")) { int v = atoi(e); if (v >= 64) g_norm_tile_elems = v; }
 }
+static void init_tuning() { std::call_once(g_tuning_once, init_tuning_once); }
 
 // ---- launch trace -----------------------------------------------------------------------------------------------
 namespace {
@@ -69,6 +74,7 @@ std::atomic<bool> g_tracing{false};
 bool trace_on() { return g_tracing.load(std::memory_order_relaxed); }
 
 void trace_before(cudaStream_t stream, const char* mangled) {
+  g_trace_mu.lock();                                // released by trace_after: a launch's two records stay adjacent
   if (g_trace_used >= g_trace.size()) return;       // capacity reached: later launches go unrecorded
   TraceRec& r = g_trace[g_trace_used];
   int st = 0;
@@ -79,9 +85,11 @@ void trace_before(cudaStream_t stream, const char* mangled) {
 }
 
 void trace_after(cudaStream_t stream) {
-  if (g_trace_used >= g_trace.size()) return;
-  cudaEventRecord(g_trace[g_trace_used].b, stream);
-  g_trace_used++;
+  if (g_trace_used < g_trace.size()) {
+    cudaEventRecord(g_trace[g_trace_used].b, stream);
+    g_trace_used++;
+  }
+  g_trace_mu.unlock();
 }
 
 bool pdl_enabled() {
@@ -119,6 +127,7 @@ int grid_for(int ntiles) {
 namespace {
 
 constexpr int kSlots = 64;
+constexpr size_t kSpareCapBytes = 16u << 20;
 constexpr int kMaxDevices = 64;
 
 struct Slot {
@@ -189,8 +198,8 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 }  // namespace
 
 CallGuard::CallGuard(int dev) : status(0), prev_device(-1), device(dev) {
-  g_mu.lock();
-  if (dev < 0 || dev >= kMaxDevices) { status = set_error("invalid device ordinal %d", dev); return; }
+  if (dev < 0 || dev >= kMaxDevices) { device = -1; status = set_error("invalid device ordinal %d", dev); return; }
+  g_dev_mu[dev].lock();
   cudaError_t e = cudaGetDevice(&prev_device);
   if (e != cudaSuccess) { status = set_error("CUDA error: %s (cudaGetDevice)", cudaGetErrorString(e)); return; }
   if (prev_device != dev) {
@@ -199,8 +208,9 @@ CallGuard::CallGuard(int dev) : status(0), prev_device(-1), device(dev) {
   }
 }
 CallGuard::~CallGuard() {
+  if (device < 0) return;
   if (prev_device >= 0 && prev_device != device) cudaSetDevice(prev_device);
-  g_mu.unlock();
+  g_dev_mu[device].unlock();
 }
 
 static DevCtx* ctx_for_current_device(int device) {
@@ -219,7 +229,7 @@ int check_common(const b200mt_lists* L, int chunk_size) {
 
 namespace {
 
-struct ImageLayout { size_t off_ptrs, off_numel, off_prefix, bytes; long long ntiles; };
+struct ImageLayout { size_t off_ptrs, off_numel, off_prefix, bytes; long long ntiles; int nonempty; };
 
 // Builds the table image for (ptrs, numel) under `tiling` in the calling thread's staging buffer.
 int build_image(const void* const* ptrs, const int64_t* numel, int D, int T, const Tiling& tiling, ImageLayout* lay,
@@ -235,9 +245,11 @@ int build_image(const void* const* ptrs, const int64_t* numel, int D, int T, con
   memcpy(img + lay->off_numel, numel, (size_t)T * 8);
   int* prefix = reinterpret_cast<int*>(img + lay->off_prefix);
   long long acc = 0;
+  int nonempty = 0;
   for (int t = 0; t < T; t++) {
     const long long n = numel[t];
     B200MT_CHECK(n >= 0, "negative numel for tensor %d", t);
+    nonempty += n > 0 ? 1 : 0;
     if (n > 0)
       for (int d = 0; d < D; d++)
         B200MT_CHECK(ptrs[(size_t)d * T + t] != nullptr, "NULL data pointer (list %d, tensor %d)", d, t);
@@ -252,6 +264,7 @@ int build_image(const void* const* ptrs, const int64_t* numel, int D, int T, con
   h->depth = D; h->ntensors = T; h->tile_elems = tiling.tile_elems; h->ppc = tiling.ppc;
   h->ntiles = (uint32_t)acc; h->chunk_elems = tiling.chunk_elems;
   lay->ntiles = acc;
+  lay->nonempty = nonempty;
   *image = img;
   return 0;
 }
@@ -314,6 +327,7 @@ void fill_view(const Slot* slot, const ImageLayout& lay, int T, const Tiling& ti
   out->tile_prefix = reinterpret_cast<const int*>(slot->dev + lay.off_prefix);
   out->ntensors = T;
   out->ntiles = (int)lay.ntiles;
+  out->nonempty = lay.nonempty;
   out->tile_elems = tiling.tile_elems;
   out->ppc = tiling.ppc;
   out->chunk_elems = tiling.chunk_elems;
@@ -453,15 +467,18 @@ int acquire_scratch(cudaStream_t stream, size_t bytes, void** out) {
     s.ptr = nullptr; s.cap = 0;
     B200MT_CUDA(cudaMalloc(&s.ptr, cap));
     s.cap = cap;
-    B200MT_CUDA(cudaMemsetAsync(s.ptr, 0, 256, stream));
+    B200MT_CUDA(cudaMemsetAsync(s.ptr, 0, kScratchZeroBytes, stream));
   }
-  if (!capturing && ctx->spare.cap < s.cap) {
-    // keep one unassigned buffer as large as the largest in use, for a stream that shows up already capturing
+  // keep one small unassigned buffer for a stream that shows up already capturing (no allocation is possible then).
+  // Capped: mirroring the largest buffer in use would double the scratch of Llama-sized norm calls for a rare case;
+  // a capture that needs more is told to warm up on the capture stream (message above).
+  const size_t spare_want = s.cap < kSpareCapBytes ? s.cap : kSpareCapBytes;
+  if (!capturing && ctx->spare.cap < spare_want) {
     if (ctx->spare.ptr) ctx->retired.push_back(ctx->spare.ptr);
     ctx->spare = StreamScratch();
-    B200MT_CUDA(cudaMalloc(&ctx->spare.ptr, s.cap));
-    ctx->spare.cap = s.cap;
-    B200MT_CUDA(cudaMemset(ctx->spare.ptr, 0, 256));
+    B200MT_CUDA(cudaMalloc(&ctx->spare.ptr, spare_want));
+    ctx->spare.cap = spare_want;
+    B200MT_CUDA(cudaMemset(ctx->spare.ptr, 0, kScratchZeroBytes));
   }
   *out = s.ptr;
   return 0;
@@ -561,6 +578,7 @@ extern "C" int b200mt_shutdown(void) {
   int prev = -1;
   cudaGetDevice(&prev);
   for (int d = 0; d < kMaxDevices; d++) {
+    std::lock_guard<std::recursive_mutex> dlk(g_dev_mu[d]);
     DevCtx* c = g_ctx[d];
     if (!c) continue;
     cudaSetDevice(d);

@@ -61,8 +61,11 @@ int acquire_table(const b200mt_lists* L, int expect_depth_min, int expect_depth_
                   const Tiling& tiling, cudaStream_t stream, TableView* out);
 
 // Per-(device, stream) scratch of at least `bytes` bytes, 256-byte aligned, contents undefined
-// except for the first 256 bytes which are zero at creation and which every user must leave
-// zero (they hold self-resetting completion counters).
+// except for the first kScratchZeroBytes bytes which are zero at creation and which every user must leave
+// zero (they hold self-resetting completion counters: 256 bytes of list-level counters, then one tile ticket per
+// tensor for the single-launch norms).
+constexpr int kNormTicketCap = 65536;
+constexpr size_t kScratchZeroBytes = 256 + sizeof(unsigned) * (size_t)kNormTicketCap;
 int acquire_scratch(cudaStream_t stream, size_t bytes, void** out);
 
 // ---- launch trace (b200mt_trace_begin / _end): when on, every kernel launch of the library is bracketed by a pair

@@ -9,30 +9,36 @@
 // bitwise reproducible run to run.  Replaces cleanup / cleanup_v3 of the reference
 // (csrc/multi_tensor_l2norm_kernel.cu:198-237) and its 320-slot accumulate-across-launches scheme.
 #pragma once
+#include <cstdlib>
+
 #include "mt_host.h"
 
 namespace b200mt {
 
-// Scratch layout used by the norm ops (floats after the 256-byte counter zone):
-//   counters[0] = ticket, counters[1] = bad-chunk flag   (both self-resetting)
+// Scratch layout used by the norm ops (floats after the zero zone):
+//   counters[0] = ticket, counters[1] = bad-chunk flag   (256 bytes, both self-resetting)
+//   tickets[kNormTicketCap]      per-tensor tile counters of the single-launch path (self-resetting; the whole zone
+//                                [0, kScratchZeroBytes) is zeroed when a scratch buffer is created and every user leaves it zero)
 //   partials[nsets][ntiles]      per-tile sums of squares
 //   totals[nsets][ntensors]      per-tensor sums of squares
 //   norms[nsets][ntensors]       per-tensor norms (used when the caller passes no output array)
 struct NormScratch {
   unsigned* counters;
+  unsigned* tickets;
   float* partials;
   float* totals;
   float* norms;
 };
 
 inline size_t norm_scratch_bytes(int nsets, int ntiles, int ntensors) {
-  return 256 + sizeof(float) * ((size_t)nsets * ntiles + 2 * (size_t)nsets * ntensors) + 64;
+  return kScratchZeroBytes + sizeof(float) * ((size_t)nsets * ntiles + 2 * (size_t)nsets * ntensors) + 64;
 }
 
 inline NormScratch carve_norm_scratch(void* base, int nsets, int ntiles, int ntensors) {
   NormScratch s;
   s.counters = reinterpret_cast<unsigned*>(base);
-  s.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(base) + 256);
+  s.tickets = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(base) + 256);
+  s.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(base) + kScratchZeroBytes);
   s.totals = s.partials + (size_t)nsets * ntiles;
   s.norms = s.totals + (size_t)nsets * ntensors;
   return s;
@@ -127,6 +133,150 @@ static __global__ void __launch_bounds__(kCleanupThreads) norm_cleanup_kernel(co
     a.counters[0] = 0;  // self-reset for the next call on this stream
     a.counters[1] = 0;
   }
+}
+
+
+// ------------------------------------------------------------------------------------------------------------------
+// Single-launch form (opt-in, see norm_fold_enabled): the second pass folded into the streaming kernel.
+//
+// The two-kernel form pays a second launch (and its drain) per norm: on a 40 us pass over 1000 x 64K elements that is
+// 10-15 % of the op.  Here every CTA, after leaving its tile's partial in the fixed slot, takes a ticket of its tensor;
+// the CTA that takes the tensor's LAST ticket re-reads all of that tensor's partials and reduces them -- in exactly the
+// order and with exactly the arithmetic of norm_cleanup_kernel, so the result does not depend on which CTA happens to
+// finish last -- and then takes a ticket of the list; the CTA that completes the last tensor forms the global norm from
+// the per-tensor totals in index order, raises the flag and resets the counters.  Still no float atomics, still
+// bitwise reproducible.  Tickets live in a zone of the scratch that is zero between calls (each finisher resets its own).
+// ------------------------------------------------------------------------------------------------------------------
+struct NormFinish {
+  CleanupArgs a;
+  unsigned* tickets;   // [ntensors]
+  int nonempty;        // tensors that own at least one tile
+  int enabled;         // 0: the op only stores partials (two-kernel form)
+};
+
+// Called by all threads of the CTA at the end of a tile; part[set] (valid in thread 0) is the tile's partial of set.
+template <int THREADS, int NSETS>
+__device__ __forceinline__ void norm_tile_done(const NormFinish& nf, int tile, int tensor, const float (&part)[NSETS], float* red) {
+  static_assert(THREADS == kCleanupThreads, "the folded second pass keeps the summation order of norm_cleanup_kernel");
+  __shared__ int s_last;
+  const CleanupArgs& a = nf.a;
+  const int tid = threadIdx.x;
+  float* partials = const_cast<float*>(a.partials);
+  if (tid == 0) {
+#pragma unroll
+    for (int set = 0; set < NSETS; set++) partials[(size_t)set * a.ntiles + tile] = part[set];
+    if (nf.enabled) {
+      __threadfence();
+      const int nt = a.tile_prefix[tensor + 1] - a.tile_prefix[tensor];
+      s_last = (atomicAdd(nf.tickets + tensor, 1u) == (unsigned)(nt - 1));
+    }
+  }
+  if (!nf.enabled) return;
+  __syncthreads();
+  if (!s_last) return;            // CTA-uniform
+  __threadfence();
+
+  // ---- this CTA completes `tensor`: chunk sums in order, per-chunk finiteness, per-tensor total
+  const int first = a.tile_prefix[tensor];
+  const int nt = a.tile_prefix[tensor + 1] - first;
+  const int nchunks = (nt + a.ppc - 1) / a.ppc;
+  bool bad = false;
+#pragma unroll
+  for (int set = 0; set < NSETS; set++) {
+    const float* p = partials + (size_t)set * a.ntiles + first;
+    float acc = 0.f;
+    for (int c = tid; c < nchunks; c += THREADS) {
+      float cs = 0.f;
+      const int j0 = c * a.ppc;
+      const int j1 = min(j0 + a.ppc, nt);
+      if (a.max_mode) {
+        for (int j = j0; j < j1; j++) cs = fmaxf(cs, __ldcg(p + j));
+        acc = fmaxf(acc, cs);
+      } else {
+        for (int j = j0; j < j1; j++) cs += __ldcg(p + j);
+        acc += cs;
+      }
+      bad = bad || !isfinite(cs);
+    }
+    const float total = a.max_mode ? cta_max<THREADS>(acc, red) : cta_sum<THREADS>(acc, red);
+    if (tid == 0) {
+      a.totals[(size_t)set * a.ntensors + tensor] = total;
+      if (float* out = a.ret_per_tensor[set]) {
+        if (!a.blend) out[tensor] = sqrtf(total);
+        else if (a.blend == 2) out[tensor] = total;
+        else if (a.max_mode) out[tensor] = a.alpha * out[tensor] + a.beta * total;
+        else out[tensor] = sqrtf(a.alpha * out[tensor] * out[tensor] + a.beta * total);
+      }
+    }
+  }
+  if (bad) atomicOr(a.counters + 1, 1u);
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    nf.tickets[tensor] = 0u;      // ready for the next call
+    s_last = (atomicAdd(a.counters, 1u) == (unsigned)(nf.nonempty - 1));
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+
+  // ---- this CTA completes the list: empty tensors, global norm in index order, flag, counter reset
+#pragma unroll
+  for (int set = 0; set < NSETS; set++) {
+    const volatile float* tot = a.totals + (size_t)set * a.ntensors;
+    float acc = 0.f;
+    for (int t = tid; t < a.ntensors; t += THREADS) {
+      const bool empty = a.tile_prefix[t + 1] == a.tile_prefix[t];
+      if (empty) {
+        if (float* out = a.ret_per_tensor[set]) {         // a tensor without elements: total 0 through the same rules
+          if (!a.blend || a.blend == 2) out[t] = 0.f;
+          else if (a.max_mode) out[t] = a.alpha * out[t];
+          else out[t] = sqrtf(a.alpha * out[t] * out[t]);
+        }
+      } else {
+        acc += tot[t];
+      }
+    }
+    if (a.ret[set]) {
+      const float total = cta_sum<THREADS>(acc, red);
+      if (tid == 0) *a.ret[set] = sqrtf(total);
+    }
+  }
+  if (tid == 0) {
+    if (*reinterpret_cast<volatile unsigned*>(a.counters + 1)) *a.noop = 1;
+    a.counters[0] = 0;
+    a.counters[1] = 0;
+  }
+}
+
+// Measured on B200 and NOT the default (profiles/norm_fold_r02.md): the ticket is an atomic whose return value the CTA
+// must wait for (~1 us through L2) at the end of every tile, on the critical path of a CTA that lives ~4 us -- 1000 x 64K
+// fp32 l2norm 60.5 -> 65.6 us, BERT-large fp16 gradient norm 124 -> 165 us.  The second launch of the two-kernel form,
+// started with programmatic dependent launch, costs less than that.  B200MT_NORM_FOLD=1 switches the folded form on
+// (it wins only where the launch itself dominates: lists of thousands of tiny tensors).
+inline bool norm_fold_enabled() {
+  static const bool on = [] { const char* e = getenv("B200MT_NORM_FOLD"); return e && atoi(e) != 0; }();
+  return on;
+}
+
+// Host side: fills the finish block of an op.  Returns true when the single-launch form applies (then the caller must
+// NOT launch norm_cleanup_kernel); false: two-kernel form (lists with more tensors than ticket slots, lists without any
+// element -- no streaming kernel is launched for those, the second pass alone writes the zeros --, B200MT_NORM_FOLD=0).
+inline bool make_norm_finish(const TableView& tv, const NormScratch& s, int nsets, int* noop, int gated, float* ret0,
+                             float* per0, float* ret1, float* per1, int nonempty, NormFinish* nf, int max_mode = 0,
+                             int blend = 0, float alpha = 0.f, float beta = 0.f) {
+  CleanupArgs& a = nf->a;
+  a.max_mode = max_mode; a.blend = blend; a.alpha = alpha; a.beta = beta;
+  a.tile_prefix = tv.tile_prefix;
+  a.ntensors = tv.ntensors; a.ntiles = tv.ntiles; a.ppc = tv.ppc; a.nsets = nsets;
+  a.partials = s.partials; a.totals = s.totals; a.counters = s.counters;
+  a.noop = noop; a.gated = gated;
+  a.ret[0] = ret0; a.ret[1] = ret1;
+  a.ret_per_tensor[0] = per0; a.ret_per_tensor[1] = per1;
+  nf->tickets = s.tickets;
+  nf->nonempty = nonempty;
+  nf->enabled = (norm_fold_enabled() && tv.ntiles > 0 && nonempty > 0 && tv.ntensors <= kNormTicketCap) ? 1 : 0;
+  return nf->enabled != 0;
 }
 
 inline int launch_norm_cleanup(const TableView& tv, const NormScratch& s, int nsets, int* noop,

@@ -69,8 +69,9 @@ struct DistAdamOp : OpBase {
   using Types = typename std::conditional<COPY, TypeList<float, float, float, Tg, Tc>, TypeList<float, float, float, Tg>>::type;
   static constexpr int NL = COPY ? 5 : 4;
   static constexpr unsigned STORES = COPY ? 0b10111 : 0b00111;
-  static constexpr int UNROLL = is_mc<Tg>::value ? B200MT_NVLS_UNROLL : B200MT_ADAM_UNROLL;
-  static constexpr int VEC = is_mc<Tg>::value ? B200MT_NVLS_VEC : B200MT_ADAM_VEC;
+  static constexpr bool MC = is_mc<Tg>::value || is_mc<Tc>::value;
+  static constexpr int UNROLL = MC ? B200MT_NVLS_UNROLL : B200MT_ADAM_UNROLL;
+  static constexpr int VEC = MC ? B200MT_NVLS_VEC : B200MT_ADAM_VEC;
   static constexpr int THREADS = 256;
   static constexpr int MIN_CTAS = (VEC * UNROLL > 8) ? 2 : 4;
   struct State { float b1, b2, eps, decay, bc1, bc2, rbc1, rbc2, rgs; };
@@ -243,6 +244,15 @@ extern "C" int b200mt_dist_adam_nvls(const b200mt_lists* L, int chunk_size, int3
                (L->dtype[4] == L->dtype[3] || L->dtype[4] == B200MT_U8),
                "dist_adam_nvls: g must be Half or BFloat16 and p_copy the same type or e5m2 bytes");
   const bool packed = L->dtype[4] == B200MT_U8;
+  // Measurement switches (tools/nvls_probe.py), carried in the upper bits of `mode`: list 3 / list 4 hold ORDINARY device
+  // addresses instead of multicast ones, i.e. the kernel keeps only one of its two collectives --
+  //   B200MT_NVLS_LOCAL_COPY:  in-switch reduction of the gradients + Adam, parameters stored locally (no broadcast)
+  //   B200MT_NVLS_LOCAL_GRADS: gradients loaded locally (no reduction) + Adam + in-switch broadcast of the parameters
+  // Three single launches whose times against the byte model say which direction of the fabric paces the full kernel.
+  const bool local_grads = (mode & B200MT_NVLS_LOCAL_GRADS) != 0, local_copy = (mode & B200MT_NVLS_LOCAL_COPY) != 0;
+  mode &= 0xff;
+  B200MT_CHECK(!(local_grads && local_copy), "dist_adam_nvls: both lists local is b200mt_dist_adam");
+  B200MT_CHECK(!(packed && (local_grads || local_copy)), "dist_adam_nvls: the measurement switches take 16-bit copies only");
   for (int t = 0; t < L->ntensors; t++) {
     B200MT_CHECK(L->numel[t] % B200MT_NVLS_VEC == 0, "dist_adam_nvls: fragment %d has %lld elements; multicast fragments "
                  "must be multiples of %d elements", t, (long long)L->numel[t], B200MT_NVLS_VEC);
@@ -263,8 +273,12 @@ extern "C" int b200mt_dist_adam_nvls(const b200mt_lists* L, int chunk_size, int3
     op.step = step; op.mode = mode;
     return launch_stream(tv, op, stream);
   };
-  if (L->dtype[3] == B200MT_BF16)
+  if (L->dtype[3] == B200MT_BF16) {
+    if (local_copy) return run(DistAdamOp<mc_bf16, __nv_bfloat16, true>());
+    if (local_grads) return run(DistAdamOp<__nv_bfloat16, mc_bf16, true>());
     return packed ? run(DistAdamOp<mc_bf16, mc_e5m2, true>()) : run(DistAdamOp<mc_bf16, mc_bf16, true>());
+  }
+  B200MT_CHECK(!(local_grads || local_copy), "dist_adam_nvls: the measurement switches are built for BFloat16 only");
   return packed ? run(DistAdamOp<mc_f16, mc_e5m2, true>()) : run(DistAdamOp<mc_f16, mc_f16, true>());
 }
 

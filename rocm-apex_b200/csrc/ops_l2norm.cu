@@ -29,7 +29,7 @@ struct L2NormOp : OpBase {
   static constexpr int UNROLL = (Elem<Tx>::SIZE == 2) ? B200MT_NORM16_UNROLL : B200MT_NORM32_UNROLL;
   static constexpr int THREADS = 256;
   struct State { float acc = 0.f; };
-  float* partials;
+  NormFinish fin;      // partial slots + the folded second pass (mt_norm.cuh)
   const int* noop;
   int gated;
   __device__ __forceinline__ bool begin(State&) const {
@@ -37,9 +37,9 @@ struct L2NormOp : OpBase {
   }
   __device__ __forceinline__ unsigned load_mask() const { return 1u; }
   __device__ __forceinline__ void elem(State& s, float (&x)[1]) const { s.acc += x[0] * x[0]; }
-  __device__ __forceinline__ void tile_end(State& s, int tile, const TileLoc&, float* smem) const {
-    const float t = cta_sum<THREADS>(s.acc, smem);
-    if (threadIdx.x == 0) partials[tile] = t;
+  __device__ __forceinline__ void tile_end(State& s, int tile, const TileLoc& L, float* smem) const {
+    const float part[1] = {cta_sum<THREADS>(s.acc, smem)};
+    norm_tile_done<THREADS, 1>(fin, tile, L.tensor, part, smem);
     s.acc = 0.f;
   }
 };
@@ -57,16 +57,16 @@ struct L2NormScaleOp : OpBase {
   static constexpr int VEC = ANY16 ? 8 : 4;
   static constexpr int THREADS = 256;
   struct State { float acc = 0.f; };
-  float* partials;
+  NormFinish fin;
   float scale;
   __device__ __forceinline__ unsigned load_mask() const { return 1u; }
   __device__ __forceinline__ void elem(State& s, float (&x)[2]) const {
     s.acc += x[0] * x[0];
     x[1] = x[0] * scale;
   }
-  __device__ __forceinline__ void tile_end(State& s, int tile, const TileLoc&, float* smem) const {
-    const float t = cta_sum<THREADS>(s.acc, smem);
-    if (threadIdx.x == 0) partials[tile] = t;
+  __device__ __forceinline__ void tile_end(State& s, int tile, const TileLoc& L, float* smem) const {
+    const float part[1] = {cta_sum<THREADS>(s.acc, smem)};
+    norm_tile_done<THREADS, 1>(fin, tile, L.tensor, part, smem);
     s.acc = 0.f;
   }
 };
@@ -90,14 +90,17 @@ extern "C" int b200mt_l2norm(const b200mt_lists* L, int chunk_size, int32_t* noo
   NormScratch ns = carve_norm_scratch(raw, 1, tv.ntiles, tv.ntensors);
   const int gated = (flags & B200MT_NORM_NOOP_GATED) ? 1 : 0;
   const char* name = gated ? "multi_tensor_l2norm_mp_cuda" : "multi_tensor_l2norm_cuda";
+  NormFinish fin;
+  const bool folded = make_norm_finish(tv, ns, 1, noop, gated, ret, ret_per_tensor, nullptr, nullptr, tv.nonempty, &fin);
   auto go = [&](auto tx) {
     L2NormOp<typename decltype(tx)::type> op;
-    op.partials = ns.partials; op.noop = noop; op.gated = gated;
+    op.fin = fin; op.noop = noop; op.gated = gated;
     return launch_stream(tv, op, stream);
   };
   // the _mp variant of the reference dispatches fp32/fp16 only (csrc/multi_tensor_l2norm_kernel_mp.cu:186);
   // bf16 is accepted here as a superset.
   if (dispatch_f32_f16_bf16(L->dtype[0], name, go)) return 1;
+  if (folded) return 0;      // the last CTA of the streaming kernel has already done the second pass
   return launch_norm_cleanup(tv, ns, 1, noop, gated, ret, ret_per_tensor, nullptr, nullptr, stream);
 }
 
@@ -113,13 +116,16 @@ extern "C" int b200mt_l2norm_scale(const b200mt_lists* L, int chunk_size, int32_
   void* raw;
   if (acquire_scratch(stream, norm_scratch_bytes(1, tv.ntiles, tv.ntensors), &raw)) return 1;
   NormScratch ns = carve_norm_scratch(raw, 1, tv.ntiles, tv.ntensors);
+  NormFinish fin;
+  const bool folded = make_norm_finish(tv, ns, 1, noop, 0, ret, ret_per_tensor, nullptr, nullptr, tv.nonempty, &fin);
   int rc = dispatch_f32_f16_bf16(L->dtype[0], "multi_tensor_l2norm_scale_cuda", [&](auto ti) {
     return dispatch_f32_f16_bf16(L->dtype[1], "multi_tensor_l2norm_scale_cuda", [&](auto to) {
       L2NormScaleOp<typename decltype(ti)::type, typename decltype(to)::type> op;
-      op.partials = ns.partials; op.scale = scale;
+      op.fin = fin; op.scale = scale;
       return launch_stream(tv, op, stream);
     });
   });
   if (rc) return 1;
+  if (folded) return 0;
   return launch_norm_cleanup(tv, ns, 1, noop, 0, ret, ret_per_tensor, nullptr, nullptr, stream);
 }

@@ -44,8 +44,7 @@ struct LambStage1Op : OpBase {
   const float* inv_scale_dev;  // MP
   const int* step_dev;         // MP
   const int* noop;
-  float* partials;             // [2][ntiles]: set 0 = p, set 1 = update
-  int ntiles;
+  NormFinish fin;              // partial slots [2][ntiles] (set 0 = p, set 1 = update) + the folded second pass
 
   __device__ __forceinline__ bool begin(State& s) const {
     s.acc_p = 0.f; s.acc_u = 0.f;
@@ -100,11 +99,12 @@ struct LambStage1Op : OpBase {
     s.acc_u += ur * ur;
     x[0] = u; x[2] = m; x[3] = v;
   }
-  __device__ __forceinline__ void tile_end(State& s, int tile, const TileLoc&, float* smem) const {
+  __device__ __forceinline__ void tile_end(State& s, int tile, const TileLoc& L, float* smem) const {
     if (!want_norms) return;
     const float tp = cta_sum<THREADS>(s.acc_p, smem);
     const float tu = cta_sum<THREADS>(s.acc_u, smem);
-    if (threadIdx.x == 0) { partials[tile] = tp; partials[(size_t)ntiles + tile] = tu; }
+    const float part[2] = {tp, tu};
+    norm_tile_done<THREADS, 2>(fin, tile, L.tensor, part, smem);
     s.acc_p = 0.f; s.acc_u = 0.f;
   }
 };
@@ -225,12 +225,13 @@ int run_lamb(const TableView& tv, const LambArgs& a, cudaStream_t stream) {
   s1.mode = a.mode; s1.bias_correction = a.bias_correction; s1.want_norms = want_norms;
   s1.global_grad_norm = a.global_grad_norm; s1.max_norm_dev = a.max_norm_dev;
   s1.inv_scale_dev = a.inv_scale_dev; s1.step_dev = a.step_dev; s1.noop = a.noop;
-  s1.partials = ns.partials; s1.ntiles = tv.ntiles;
-  if (launch_stream(tv, s1, stream)) return 1;
-
   float* pn = ns.norms;
   float* un = ns.norms + tv.ntensors;
-  if (want_norms) {
+  // per-tensor ||p|| and ||update||: reduced by the last CTA of each tensor inside stage 1 (two launches per LAMB step)
+  const bool folded = make_norm_finish(tv, ns, 2, a.noop, MP ? 1 : 0, nullptr, pn, nullptr, un, tv.nonempty, &s1.fin);
+  if (launch_stream(tv, s1, stream)) return 1;
+
+  if (want_norms && !folded) {
     // per-tensor ||p|| and ||update||; a non-finite chunk sum raises the flag, as the reference's
     // two per-tensor l2norm passes would (csrc/multi_tensor_lamb.cu:370,394)
     if (launch_norm_cleanup(tv, ns, 2, a.noop, MP ? 1 : 0, nullptr, pn, nullptr, un, stream)) return 1;

@@ -130,12 +130,14 @@ extern "C" int b200mt_l2norm_flat_noalloc(const void* x, int dtype, int64_t nume
   tv.tile_prefix = reinterpret_cast<const int*>(scratch + 272);
   tv.ntensors = 1;
   tv.ntiles = (int)ntiles;
+  tv.nonempty = numel > 0 ? 1 : 0;
   tv.tile_elems = tiling.tile_elems;
   tv.ppc = tiling.ppc;
   tv.chunk_elems = tiling.chunk_elems;
 
   NormScratch ns;
   ns.counters = reinterpret_cast<unsigned*>(scratch);
+  ns.tickets = nullptr;   // two-kernel form only
   ns.partials = reinterpret_cast<float*>(scratch + 512);
   ns.totals = ns.partials + kNoallocMaxTiles;
   ns.norms = ns.totals + 1;

@@ -92,7 +92,42 @@ PyObject* pack_lists(PyObject*, PyObject* args) {
   return Py_BuildValue("(nnNi)", T, depth, ct, (int)ref_device.index());
 }
 
+// check_rows(rows, name0, name1, grad_ptrs_addr, dtype_code) -> 0 | 1 | 2
+//   rows: list of (param, state_dict, state0, state1) as cached by apex.optimizers._common.GroupCache.
+//   0: every param has a dense, contiguous gradient of the cached dtype at the cached address AND state_dict[name0/1] are
+//      still the cached tensors  -> the prepared [g, p, s0, s1] handle may be used as it is;
+//   1: the state is unchanged but a gradient is missing, moved or changed type -> re-read the gradients;
+//   2: a state tensor was replaced -> the cache entry is stale.
+// One C loop instead of a Python loop with two dict look-ups and an attribute read per parameter.
+PyObject* check_rows(PyObject*, PyObject* args) {
+  PyObject *rows, *n0, *n1;
+  unsigned long long addr;
+  int code;
+  if (!PyArg_ParseTuple(args, "OOOKi", &rows, &n0, &n1, &addr, &code)) return nullptr;
+  if (!PyList_Check(rows)) return fail("check_rows: rows must be a list");
+  const uint64_t* want = reinterpret_cast<const uint64_t*>(addr);
+  const Py_ssize_t n = PyList_GET_SIZE(rows);
+  long rc = 0;
+  for (Py_ssize_t i = 0; i < n; i++) {
+    PyObject* row = PyList_GET_ITEM(rows, i);
+    if (!PyTuple_Check(row) || PyTuple_GET_SIZE(row) != 4) return fail("check_rows: malformed row");
+    PyObject* p = PyTuple_GET_ITEM(row, 0);
+    PyObject* st = PyTuple_GET_ITEM(row, 1);
+    if (!THPVariable_Check(p) || !PyDict_Check(st)) return fail("check_rows: malformed row");
+    if (PyDict_GetItem(st, n0) != PyTuple_GET_ITEM(row, 2) || PyDict_GetItem(st, n1) != PyTuple_GET_ITEM(row, 3))
+      return PyLong_FromLong(2);
+    if (rc) continue;
+    const at::Tensor& x = THPVariable_Unpack(p);
+    const at::Tensor& g = x.grad();
+    if (!g.defined() || g.is_sparse() || dtype_code(g.scalar_type()) != code || !g.is_contiguous() ||
+        reinterpret_cast<uint64_t>(g.data_ptr()) != want[i])
+      rc = 1;
+  }
+  return PyLong_FromLong(rc);
+}
+
 PyMethodDef methods[] = {
+    {"check_rows", check_rows, METH_VARARGS, "are the cached gradient addresses and state tensors of a parameter group still valid?"},
     {"pack_lists", pack_lists, METH_VARARGS, "tensor lists -> raw pointer / numel arrays"},
     {nullptr, nullptr, 0, nullptr}};
 

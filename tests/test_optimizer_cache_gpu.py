@@ -136,3 +136,57 @@ def test_fused_sgd_memo_matches_uncached_steps_and_torch():
     set_grads(a, b, 50)
     cached.step(); fresh._sets.clear(); fresh.step()
     assert same(a, b, tol=0.0)
+
+
+def test_fused_adam_prepared_handle_follows_the_gradients():
+    """FusedAdam hands its kernel a prepared list handle while the gradients stay where they were (one C loop checks the
+    addresses and the state tensors), re-prepares when they move, gives up preparing a bucket that moves every step, and
+    never uses a stale address: stepped next to torch.optim.AdamW through all of it."""
+    import _b200mt as mt
+    from apex.optimizers import FusedAdam
+    if mt.check_rows is None:
+        pytest.skip("native packer not built")
+    kw = dict(lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=0.01)
+    x, y = make(seed=3)
+    fx, ty = FusedAdam(x, **kw), torch.optim.AdamW(y, **kw)
+    handle = lambda: fx._lists.groups[0][4][0][4].get("prep")
+    g = torch.Generator(device="cuda").manual_seed(5)
+    for p, q in zip(x, y):
+        p.grad = torch.randn(p.shape, generator=g, device="cuda")
+        q.grad = p.grad.clone()
+    fx.step(); ty.step()
+    first = handle()
+    assert first is not None and first.keep is None
+    up0, hit0 = mt.lib.b200mt_table_uploads(), mt.lib.b200mt_table_hits()
+    for it in range(4):                                   # gradients rewritten in place: same addresses, same handle
+        for p, q in zip(x, y):
+            p.grad.copy_(torch.randn(p.shape, generator=g, device="cuda"))
+            q.grad.copy_(p.grad)
+        fx.step(); ty.step()
+        assert same(x, y, tol=1e-5) and handle() is first
+    assert mt.lib.b200mt_table_uploads() == up0 and mt.lib.b200mt_table_hits() == hit0 + 4
+    # one gradient moves: the handle is rebuilt, results still right
+    x[2].grad = torch.randn(x[2].shape, generator=g, device="cuda"); y[2].grad = x[2].grad.clone()
+    fx.step(); ty.step()
+    assert same(x, y, tol=1e-5) and handle() is not first and handle() is not None
+    # a state tensor replaced by the user: noticed (rc 2), the new tensor is used
+    fx.state[x[1]]["exp_avg"] = fx.state[x[1]]["exp_avg"].clone()
+    ty_state = ty.state[y[1]]["exp_avg"]
+    fx.step(); ty.step()
+    assert same(x, y, tol=1e-5) and ty_state is ty.state[y[1]]["exp_avg"]
+    # gradients that land somewhere else every step: after three misses the bucket goes back to plain lists
+    keep = []
+    for it in range(5):
+        for p, q in zip(x, y):
+            p.grad = torch.randn(p.shape, generator=g, device="cuda"); q.grad = p.grad.clone()
+            keep.append(p.grad)                           # held, so the allocator cannot hand the address out again
+        fx.step(); ty.step()
+        assert same(x, y, tol=1e-5)
+    assert handle() is None
+    # a parameter without gradient this step, then with one again
+    x[0].grad, y[0].grad = None, None
+    fx.step(); ty.step()
+    for p, q in zip(x, y):
+        p.grad = torch.randn(p.shape, generator=g, device="cuda"); q.grad = p.grad.clone()
+    fx.step(); ty.step()
+    assert same(x[1:], y[1:], tol=1e-5)

@@ -151,7 +151,7 @@ def test_launch_trace_names_and_times_every_kernel():
         amp_C.multi_tensor_l2norm(CHUNK, f, [g], False)
         amp_C.multi_tensor_adam(CHUNK, f, [g, p, m, v], 1e-3, 0.9, 0.999, 1e-8, 1, 1, 1, 0.0)
     names = [n for n, _ in tr.launches]
-    assert len(names) == 4, names
+    assert len(names) == 4, names      # the norm is two kernels (B200MT_NORM_FOLD=1 would make it one)
     assert "ScaleOp" in names[0] and "L2NormOp" in names[1] and "norm_cleanup" in names[2] and "AdamOp" in names[3]
     assert all(0.0 < ms < 5.0 for _, ms in tr.launches), tr.launches
     # tracing is off again: nothing is recorded, results unchanged

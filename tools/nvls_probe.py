@@ -61,6 +61,25 @@ def main():
                                            ep.data_ptr(), wd.data_ptr(), 1e-4, float(world), step[0], 1, sp))
         hp.barrier(channel=1)
 
+    # the fused kernel with only ONE of its two collectives (include/b200mt.h: B200MT_NVLS_LOCAL_COPY / _LOCAL_GRADS)
+    g_loc = g[rank * shard:(rank + 1) * shard]
+    L_fa = mt.pack([[p32], [m32], [v32], [g_mc], [out]], 5)       # reduce in the switch, store locally
+    L_fb = mt.pack([[p32], [m32], [v32], [g_loc], [p_mc]], 5)     # load locally, broadcast through the switch
+
+    def fused_form(L, flag_bits):
+        def run():
+            step[0] += 1
+            hg.barrier(channel=0)
+            mt.check(lib.b200mt_dist_adam_nvls(L.ref(), 65536, flag.data_ptr(), b1.data_ptr(), b2.data_ptr(), bc.data_ptr(),
+                                               ep.data_ptr(), wd.data_ptr(), 1e-4, float(world), step[0], 1 | flag_bits, sp))
+            hp.barrier(channel=1)
+        return run
+
+    fused_reduce_only, fused_bcast_only = fused_form(L_fa, 0x200), fused_form(L_fb, 0x100)
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    from nvlink_counters import NvlinkCounters
+    nvl = NvlinkCounters(dev.index)
+
     def timed(fn, reps=4):
         fn(); fn(); torch.cuda.synchronize(); dist.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -71,6 +90,30 @@ def main():
         t = torch.tensor([e0.elapsed_time(e1) / reps], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t)
 
+    # ---- which direction paces the fused step?  three single launches + the links' own byte counters
+    forms = {}
+    for name, fn in (("full", fused), ("reduce_only_local_store", fused_reduce_only), ("broadcast_only_local_load", fused_bcast_only),
+                     ("standalone_rs", rs), ("standalone_ag", ag)):
+        reps = 4
+        fn(); fn(); torch.cuda.synchronize(); dist.barrier()
+        before = nvl.read() if nvl.ok else None
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record(); torch.cuda.synchronize(); dist.barrier()
+        d = nvl.delta(before) if nvl.ok else [0, 0]
+        t = torch.tensor([e0.elapsed_time(e1) / reps, d[0] / reps, d[1] / reps], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+        forms[name] = {"ms": round(ms, 3), "tx_GB": round(float(t[1]) / 1e9, 3), "rx_GB": round(float(t[2]) / 1e9, 3),
+                       "tx_GBs": round(float(t[1]) / ms / 1e6, 1), "rx_GBs": round(float(t[2]) / ms / 1e6, 1)}
+    if rank == 0:
+        print(json.dumps({"world": world, "elems": total, "model_out_GB_full": round((2.0 * total + 2.0 * shard) / 1e9, 3),
+                          "nvlink_counters": nvl.ok, "forms": forms}), flush=True)
+    if os.environ.get("PROBE_FORMS_ONLY"):
+        dist.destroy_process_group()
+        return
     res = []
     for tile, cap in [(4096, 0), (16384, 0), (65536, 0), (262144, 0), (1048576, 0), (16384, 148 * 2), (65536, 148 * 2)]:
         mt.check(lib.b200mt_set_tuning(tile, cap))
