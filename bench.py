@@ -271,7 +271,7 @@ def cold_leg(mt, lib, dev, stream, L_scale, L_adam, fp, nparams, peak, reps=20):
             ("scale", 8.0 * nparams, lambda k: lib.b200mt_scale(L_scale.ref(), CHUNK, fp, 1.0, sp)),
             ("adam", 28.0 * nparams, lambda k: lib.b200mt_adam(L_adam.ref(), CHUNK, fp, ADAM["lr"], ADAM["beta1"], ADAM["beta2"],
                                                              ADAM["eps"], 1000 + k, 1, 1, ADAM["wd"], 1.0, sp))):
-        ts = []
+        ts, inc = [], []
         for k in range(reps + 2):
             flush.fill_(float(k))
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -281,10 +281,28 @@ def cold_leg(mt, lib, dev, stream, L_scale, L_adam, fp, nparams, peak, reps=20):
             torch.cuda.synchronize()
             if k >= 2:
                 ts.append(e0.elapsed_time(e1))
+        # the same launch queued right behind the flush (its launch latency hides behind the flush, as behind any
+        # predecessor in a real step): time(flush; op) - time(flush)
+        for k in range(reps + 2):
+            a0, a1, a2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            flush.fill_(float(k))          # keeps the GPU busy while the rest is queued: no launch gap inside either interval
+            a0.record(stream)
+            flush.fill_(float(k + 1))
+            a1.record(stream)
+            flush.fill_(float(k + 2))
+            mt.check(call(k))
+            a2.record(stream)
+            torch.cuda.synchronize()
+            if k >= 2:
+                inc.append(a1.elapsed_time(a2) - a0.elapsed_time(a1))
         t = sum(ts) / len(ts)
+        ti = statistics.median(inc)
         out[name] = {"avg_launch_ms": t, "median_launch_ms": statistics.median(ts), "achieved_gbs": nbytes / (t * 1e-3) / 1e9,
-                     "frac": nbytes / (t * 1e-3) / 1e9 / peak, "bytes_per_launch": nbytes}
-    out["what"] = "each launch timed alone (CUDA events) right after a 512 MiB write that evicts the 126 MB L2"
+                     "frac": nbytes / (t * 1e-3) / 1e9 / peak, "bytes_per_launch": nbytes,
+                     "behind_flush_ms": ti, "behind_flush_frac": nbytes / (ti * 1e-3) / 1e9 / peak}
+    out["what"] = ("each launch timed alone (CUDA events on either side: includes the ~5 us launch latency of an idle stream) right after "
+                   "a 512 MiB write that evicts the 126 MB L2; behind_flush_* = the same launch queued directly behind such a write, "
+                   "time(write; op) - time(write): the kernel's own cold-cache time")
     del flush
     return out
 

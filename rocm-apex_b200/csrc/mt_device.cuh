@@ -27,6 +27,7 @@ struct TableView {
   int       ntensors;
   int       ntiles;
   int       nonempty;     // tensors with at least one element
+  int       multichunk;   // tensors longer than one chunk
   int       tile_elems;   // elements per scheduling tile
   int       ppc;          // tiles per full chunk (1 for element-wise ops)
   long long chunk_elems;  // chunk length in elements (== tile_elems when ppc == 1)

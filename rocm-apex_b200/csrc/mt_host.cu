@@ -229,7 +229,7 @@ int check_common(const b200mt_lists* L, int chunk_size) {
 
 namespace {
 
-struct ImageLayout { size_t off_ptrs, off_numel, off_prefix, bytes; long long ntiles; int nonempty; };
+struct ImageLayout { size_t off_ptrs, off_numel, off_prefix, bytes; long long ntiles; int nonempty, multichunk; };
 
 // Builds the table image for (ptrs, numel) under `tiling` in the calling thread's staging buffer.
 int build_image(const void* const* ptrs, const int64_t* numel, int D, int T, const Tiling& tiling, ImageLayout* lay,
@@ -245,11 +245,12 @@ int build_image(const void* const* ptrs, const int64_t* numel, int D, int T, con
   memcpy(img + lay->off_numel, numel, (size_t)T * 8);
   int* prefix = reinterpret_cast<int*>(img + lay->off_prefix);
   long long acc = 0;
-  int nonempty = 0;
+  int nonempty = 0, multichunk = 0;
   for (int t = 0; t < T; t++) {
     const long long n = numel[t];
     B200MT_CHECK(n >= 0, "negative numel for tensor %d", t);
     nonempty += n > 0 ? 1 : 0;
+    multichunk += n > tiling.chunk_elems ? 1 : 0;
     if (n > 0)
       for (int d = 0; d < D; d++)
         B200MT_CHECK(ptrs[(size_t)d * T + t] != nullptr, "NULL data pointer (list %d, tensor %d)", d, t);
@@ -265,6 +266,7 @@ int build_image(const void* const* ptrs, const int64_t* numel, int D, int T, con
   h->ntiles = (uint32_t)acc; h->chunk_elems = tiling.chunk_elems;
   lay->ntiles = acc;
   lay->nonempty = nonempty;
+  lay->multichunk = multichunk;
   *image = img;
   return 0;
 }
@@ -328,6 +330,7 @@ void fill_view(const Slot* slot, const ImageLayout& lay, int T, const Tiling& ti
   out->ntensors = T;
   out->ntiles = (int)lay.ntiles;
   out->nonempty = lay.nonempty;
+  out->multichunk = lay.multichunk;
   out->tile_elems = tiling.tile_elems;
   out->ppc = tiling.ppc;
   out->chunk_elems = tiling.chunk_elems;

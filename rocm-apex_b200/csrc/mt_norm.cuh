@@ -62,12 +62,37 @@ struct CleanupArgs {
   int max_mode;
   int blend;
   float alpha, beta;
+  int nbatch;    // norm_cleanup_kernel: CTAs [0, nbatch) handle the one-chunk tensors, 1024 each
+  int tickets;   // ... and this many CTAs take part in the last-one-done count: nbatch + the multi-chunk tensors
 };
+
+// One tensor's result from its total (sum of squares, or max): per-tensor output rules shared by every path.
+__device__ __forceinline__ void norm_store_tensor(const CleanupArgs& a, int set, int t, float total) {
+  a.totals[(size_t)set * a.ntensors + t] = total;
+  if (float* out = a.ret_per_tensor[set]) {
+    if (!a.blend) out[t] = sqrtf(total);
+    else if (a.blend == 2) out[t] = total;   // raw sum of squares: the caller all-reduces before the sqrt
+    else if (a.max_mode) out[t] = a.alpha * out[t] + a.beta * total;
+    else out[t] = sqrtf(a.alpha * out[t] * out[t] + a.beta * total);
+  }
+}
+
+// Second pass.  Tensors are treated by size, always with the SAME arithmetic -- chunk sums in tile order, chunk c
+// accumulated by thread c mod 256, the xor-shuffle tree of cta_sum -- so that the value does not depend on the path
+// taken (nor on the folded form of norm_tile_done):
+//   one chunk or none  (tensor <= chunk_size)   one THREAD per tensor, 1024 tensors per "batch" CTA (CTAs [0, nbatch))
+//   2..32 chunks                                  a CTA per tensor (CTAs [nbatch, nbatch + T)), warp 0 works: lane c = chunk c
+//   more                                          a CTA per tensor, thread-strided, cta_sum
+// A per-tensor CTA whose tensor has at most one chunk leaves at once (the batch CTAs own it) and takes no ticket; when the
+// list has no multi-chunk tensor those CTAs are not launched at all.  Round 1 gave every tensor a CTA: on a list of 1000
+// one-chunk tensors that was 1000 CTAs in which one thread worked and 255 went through two barriers, a fence and a ticket --
+// 13 us for 32 KB of partials (ncu, profiles/light_r02_summary.md).  Such a list is now ONE CTA: no ticket, no fence.
+constexpr int kBatchTensors = 1024;
 
 static __global__ void __launch_bounds__(kCleanupThreads) norm_cleanup_kernel(const CleanupArgs a) {
   __shared__ float red[kCleanupThreads / 32];
   __shared__ int s_last;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31;
   // launched with programmatic stream serialization: this grid may become resident while pass 1 drains its last wave;
   // everything it reads (partials, the flag) is produced by pass 1, so wait for that kernel to complete and flush first
   asm volatile("griddepcontrol.launch_dependents;");
@@ -75,11 +100,49 @@ static __global__ void __launch_bounds__(kCleanupThreads) norm_cleanup_kernel(co
   const bool skip = a.gated && (*reinterpret_cast<volatile int*>(a.noop) != 0);
   bool bad = false;
 
-  if (!skip) {
-    for (int t = blockIdx.x; t < a.ntensors; t += gridDim.x) {
+  if ((int)blockIdx.x < a.nbatch) {
+    // ---- batch CTA: every tensor of its range that has one chunk or none, one thread each
+    const int t1 = min(a.ntensors, ((int)blockIdx.x + 1) * kBatchTensors);
+    for (int t = blockIdx.x * kBatchTensors + tid; !skip && t < t1; t += kCleanupThreads) {
       const int first = a.tile_prefix[t];
       const int nt = a.tile_prefix[t + 1] - first;
-      const int nchunks = (nt + a.ppc - 1) / a.ppc;
+      if (nt > a.ppc) continue;                    // more than one chunk: its own CTA
+      for (int set = 0; set < a.nsets; set++) {
+        const float* p = a.partials + (size_t)set * a.ntiles + first;
+        float cs = 0.f;
+        if (a.max_mode) { for (int j = 0; j < nt; j++) cs = fmaxf(cs, p[j]); }
+        else { for (int j = 0; j < nt; j++) cs += p[j]; }
+        bad = bad || !isfinite(cs);
+        norm_store_tensor(a, set, t, a.max_mode ? fmaxf(0.f, cs) : 0.f + cs);
+      }
+    }
+  } else {
+    const int t = blockIdx.x - a.nbatch;
+    const int first = a.tile_prefix[t];
+    const int nt = a.tile_prefix[t + 1] - first;
+    if (nt <= a.ppc) return;                       // CTA-uniform; not counted among the tickets
+    const int nchunks = (nt + a.ppc - 1) / a.ppc;
+    if (!skip && nchunks <= 32) {
+      // ---- warp 0: lane c holds chunk c
+      if (tid < 32) {
+        for (int set = 0; set < a.nsets; set++) {
+          const float* p = a.partials + (size_t)set * a.ntiles + first;
+          float acc = 0.f;
+          if (lane < nchunks) {
+            float cs = 0.f;
+            const int j0 = lane * a.ppc, j1 = min(j0 + a.ppc, nt);
+            if (a.max_mode) { for (int j = j0; j < j1; j++) cs = fmaxf(cs, p[j]); acc = fmaxf(acc, cs); }
+            else { for (int j = j0; j < j1; j++) cs += p[j]; acc += cs; }
+            bad = bad || !isfinite(cs);
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1)
+            acc = a.max_mode ? fmaxf(acc, __shfl_xor_sync(0xffffffffu, acc, o)) : acc + __shfl_xor_sync(0xffffffffu, acc, o);
+          if (lane == 0) norm_store_tensor(a, set, t, acc);
+        }
+      }
+    } else if (!skip) {
+      // ---- the whole CTA
       for (int set = 0; set < a.nsets; set++) {
         const float* p = a.partials + (size_t)set * a.ntiles + first;
         float acc = 0.f;
@@ -97,27 +160,24 @@ static __global__ void __launch_bounds__(kCleanupThreads) norm_cleanup_kernel(co
           bad = bad || !isfinite(cs);
         }
         const float total = a.max_mode ? cta_max<kCleanupThreads>(acc, red) : cta_sum<kCleanupThreads>(acc, red);
-        if (tid == 0) {
-          a.totals[(size_t)set * a.ntensors + t] = total;
-          if (float* out = a.ret_per_tensor[set]) {
-            if (!a.blend) out[t] = sqrtf(total);
-            else if (a.blend == 2) out[t] = total;   // raw sum of squares: the caller all-reduces before the sqrt
-            else if (a.max_mode) out[t] = a.alpha * out[t] + a.beta * total;
-            else out[t] = sqrtf(a.alpha * out[t] * out[t] + a.beta * total);
-          }
-        }
+        if (tid == 0) norm_store_tensor(a, set, t, total);
       }
     }
-    if (bad) atomicOr(a.counters + 1, 1u);
   }
+  if (bad) atomicOr(a.counters + 1, 1u);
 
-  // ---- last CTA done: global norm from the per-tensor totals, in index order
-  __threadfence();
-  __syncthreads();
-  if (tid == 0) s_last = (atomicAdd(a.counters, 1u) == gridDim.x - 1);
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
+  // ---- global norm from the per-tensor totals, in index order: by this CTA if it is the only one with work, else by the
+  // last one to finish (a.tickets CTAs take a ticket: the batch CTAs and the CTAs of the multi-chunk tensors)
+  if (a.tickets > 1) {
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = (atomicAdd(a.counters, 1u) == (unsigned)(a.tickets - 1));
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+  } else {
+    __syncthreads();       // one CTA: its own global writes (totals, the bad flag) are visible to all its threads
+  }
   if (!skip) {
     for (int set = 0; set < a.nsets; set++) {
       if (!a.ret[set]) continue;
@@ -134,7 +194,6 @@ static __global__ void __launch_bounds__(kCleanupThreads) norm_cleanup_kernel(co
     a.counters[1] = 0;
   }
 }
-
 
 // ------------------------------------------------------------------------------------------------------------------
 // Single-launch form (opt-in, see norm_fold_enabled): the second pass folded into the streaming kernel.
@@ -273,6 +332,7 @@ inline bool make_norm_finish(const TableView& tv, const NormScratch& s, int nset
   a.noop = noop; a.gated = gated;
   a.ret[0] = ret0; a.ret[1] = ret1;
   a.ret_per_tensor[0] = per0; a.ret_per_tensor[1] = per1;
+  a.nbatch = 0; a.tickets = 0;     // fields of the two-kernel second pass only
   nf->tickets = s.tickets;
   nf->nonempty = nonempty;
   nf->enabled = (norm_fold_enabled() && tv.ntiles > 0 && nonempty > 0 && tv.ntensors <= kNormTicketCap) ? 1 : 0;
@@ -291,7 +351,9 @@ inline int launch_norm_cleanup(const TableView& tv, const NormScratch& s, int ns
   a.noop = noop; a.gated = gated;
   a.ret[0] = ret0; a.ret[1] = ret1;
   a.ret_per_tensor[0] = per0; a.ret_per_tensor[1] = per1;
-  int grid = tv.ntensors < 2048 ? tv.ntensors : 2048;
+  a.nbatch = (tv.ntensors + kBatchTensors - 1) / kBatchTensors;
+  a.tickets = a.nbatch + tv.multichunk;
+  const int grid = a.nbatch + (tv.multichunk > 0 ? tv.ntensors : 0);
   const bool tracing = trace_on();
   if (tracing) trace_before(stream, "norm_cleanup_kernel");
   if (pdl_enabled() && !tracing) {

@@ -131,6 +131,7 @@ extern "C" int b200mt_l2norm_flat_noalloc(const void* x, int dtype, int64_t nume
   tv.ntensors = 1;
   tv.ntiles = (int)ntiles;
   tv.nonempty = numel > 0 ? 1 : 0;
+  tv.multichunk = numel > tiling.chunk_elems ? 1 : 0;
   tv.tile_elems = tiling.tile_elems;
   tv.ppc = tiling.ppc;
   tv.chunk_elems = tiling.chunk_elems;
