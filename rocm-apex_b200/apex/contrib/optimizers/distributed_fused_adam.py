@@ -307,7 +307,9 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                     p.data = v
         self._ag_pg = self._pg
         if self._cuda:
-            self._comm_stream = torch.cuda.Stream(device=dev)
+            # high priority: a collective started from a gradient hook must get SMs while backward's kernels keep the GPU
+            # full, otherwise it only advances in the gaps and nothing is hidden (tools/bench_overlap.py)
+            self._comm_stream = torch.cuda.Stream(device=dev, priority=-1)
             self._ag_stream = self._comm_stream
             self._rs_done = [torch.cuda.Event() for _ in range(K)]
             self._adam_done = [torch.cuda.Event() for _ in range(K)]
@@ -319,7 +321,7 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                 # behind them on one communicator.  Only when the optimizer spans the whole job: new_group() is
                 # collective over the default group.
                 self._ag_pg = dist.new_group(ranks=list(range(W)))
-                self._ag_stream = torch.cuda.Stream(device=dev)
+                self._ag_stream = torch.cuda.Stream(device=dev, priority=-1)
         # overlapped reductions (reference :158-164,381-395,489-502): a hook per parameter marks its gradient
         # as produced; pipeline chunks are flushed (flattened + reduce-scattered on the side stream) from the
         # LAST chunk down, each as soon as every parameter that touches it has its gradient -- backward

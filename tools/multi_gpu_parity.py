@@ -151,7 +151,7 @@ def sharded_adam_parity(opt, sample_elems=16 << 20):
     pc_ref = [torch.zeros(x["n"], dtype=copy_dt, device=dev) for x in rows]
     pc_ideal = [torch.zeros(x["n"], dtype=copy_dt, device=dev) for x in rows]
     res = {"master_p_m_v_max_rel": 0.0, "copy_vs_unsharded_max_ulp": 0, "reduced_grad_max_err_over_sum_abs": 0.0,
-           "reduced_grad_vs_rn_fp32_sum_max_ulp": 0, "copy_vs_fp32_allreduce_path_max_ulp": 0, "elements_checked": 0}
+           "reduced_grad_vs_rn_fp32_sum_max_ulp": 0, "elements_checked": 0}
     pa, ma, va = ([t.clone() for t in l] for l in (p0, m0, v0))
     gideal = [s_.to(low) for s_ in gsum]
     if rows:
@@ -169,11 +169,15 @@ def sharded_adam_parity(opt, sample_elems=16 << 20):
             res["master_p_m_v_max_rel"] = max(res["master_p_m_v_max_rel"], max_rel(got, want))
         if not fused:
             res["copy_vs_unsharded_max_ulp"] = max(res["copy_vs_unsharded_max_ulp"], ulp_diff16(opt._fp16_p[sl], pc_ref[i]))
-        res["reduced_grad_vs_rn_fp32_sum_max_ulp"] = max(res["reduced_grad_vs_rn_fp32_sum_max_ulp"], ulp_diff16(gred[i], gideal[i]))
-        res["copy_vs_fp32_allreduce_path_max_ulp"] = max(res["copy_vs_fp32_allreduce_path_max_ulp"],
-                                                         ulp_diff16(opt._new_params[x["flat"]:x["flat"] + x["n"]], pc_ideal[i]))
-        res["master_p_vs_fp32_allreduce_path_max_rel"] = max(res.get("master_p_vs_fp32_allreduce_path_max_rel", 0.0),
-                                                             max_rel(opt._fp32_p[sl], p0[i]))
+        # informational (not bounded): against ONE rounding of the fp32 sum.  ulps only where the sum is not a cancellation
+        # (|sum| >= sum|g_i| / 4: elsewhere a 16-bit ulp of the tiny result says nothing), and how many elements of the
+        # low-precision copy come out identical to that path
+        solid = gsum[i].abs() >= 0.25 * gabs[i]
+        if bool(solid.any()):
+            res["reduced_grad_vs_rn_fp32_sum_max_ulp"] = max(res["reduced_grad_vs_rn_fp32_sum_max_ulp"],
+                                                             ulp_diff16(gred[i][solid], gideal[i][solid]))
+        same = (opt._new_params[x["flat"]:x["flat"] + x["n"]] == pc_ideal[i]).sum()
+        res["copy_equal_to_fp32_allreduce_path"] = res.get("copy_equal_to_fp32_allreduce_path", 0) + int(same)
         err = (gred[i].float() - gsum[i]).abs() / gabs[i].clamp_min(1e-30)
         res["reduced_grad_max_err_over_sum_abs"] = max(res["reduced_grad_max_err_over_sum_abs"], float(err.max()))
         res["elements_checked"] += x["n"]
@@ -186,14 +190,14 @@ def sharded_adam_parity(opt, sample_elems=16 << 20):
             dist.broadcast(want, src=dist.get_global_rank(opt._pg, owner), group=opt._pg)
             res["copy_vs_unsharded_max_ulp"] = max(res["copy_vs_unsharded_max_ulp"], ulp_diff16(opt._new_params[pos:pos + n], want))
     t = torch.tensor([res["master_p_m_v_max_rel"], float(res["copy_vs_unsharded_max_ulp"]), res["reduced_grad_max_err_over_sum_abs"],
-                      float(res["reduced_grad_vs_rn_fp32_sum_max_ulp"]), float(res["copy_vs_fp32_allreduce_path_max_ulp"]),
-                      res.get("master_p_vs_fp32_allreduce_path_max_rel", 0.0)], dtype=torch.float64, device=dev)
+                      float(res["reduced_grad_vs_rn_fp32_sum_max_ulp"])], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX, group=opt._pg)
-    n = torch.tensor([float(res["elements_checked"])], dtype=torch.float64, device=dev)
+    n = torch.tensor([float(res["elements_checked"]), float(res.get("copy_equal_to_fp32_allreduce_path", 0))], dtype=torch.float64,
+                     device=dev)
     dist.all_reduce(n, group=opt._pg)
     res = {"master_p_m_v_max_rel": float(t[0]), "copy_vs_unsharded_max_ulp": int(t[1]),
            "reduced_grad_max_err_over_sum_abs": float(t[2]), "reduced_grad_vs_rn_fp32_sum_max_ulp": int(t[3]),
-           "copy_vs_fp32_allreduce_path_max_ulp": int(t[4]), "master_p_vs_fp32_allreduce_path_max_rel": float(t[5]),
+           "copy_fraction_identical_to_an_fp32_allreduce_path": float(n[1]) / max(1.0, float(n[0])),
            "elements_checked": int(n[0]), "samples_per_rank": len(rows), "step": step_no}
     # bounds: identical inputs through the sharded and the unsharded launch of the same rule -> 1e-6 on the fp32
     # state, one 16-bit ulp on the copy.  A 16-bit sum of W terms is rounded up to W-1 times on the way (NCCL ring: half
