@@ -154,9 +154,24 @@ def single_config(nparams, ntensors):
 
 def cpu_reference_run(steps, warmup, max_seconds=30.0, shapes=None):
     from oracle import mt_oracle as O
-    # torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm is meant to use all the host threads it can
+    # torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm is meant to use all the host threads it CAN use: the
+    # count is calibrated on a short probe (every thread the affinity mask allows, half, a quarter, one), because on a
+    # box whose mask is wider than its usable cores the full count runs 50x slower than half of it
     try:
-        torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
+        allowed = max(1, len(os.sched_getaffinity(0)))
+        probe = [torch.randn(200000) for _ in range(32)]
+        best = (None, 1)
+        for n in sorted({allowed, max(1, allowed // 2), max(1, allowed // 4), 1}, reverse=True):
+            torch.set_num_threads(n)
+            for rep in range(2):
+                t0 = time.perf_counter()
+                for a in probe:
+                    a.mul_(1.0001)
+                    float(a.sum())
+                dt = time.perf_counter() - t0
+            if best[0] is None or dt < best[0] * 0.9:
+                best = (dt, n)
+        torch.set_num_threads(best[1])
     except Exception:
         pass
     if shapes is None:

@@ -73,8 +73,11 @@ def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, str
             "roofline": {"bound": "nvlink", "achieved": nv_bytes / (ms * 1e-3) / 1e9, "peak": NVLINK_GBS, "unit": "GB/s",
                          "frac": nv_bytes / (ms * 1e-3) / 1e9 / NVLINK_GBS,
                          "traffic": (nvlink_measured or {}).get("tx_bytes_per_step_per_gpu"),
-                         "traffic_source": "NVLink bytes this GPU transmitted per step (NVML link counters around the timed loop), "
-                                           "the counterpart of `bytes_per_launch` for an NVLink-bound kernel",
+                         "traffic_source": ("NVLink bytes this GPU transmitted per step (NVML link counters around the timed loop), "
+                                            "the counterpart of `bytes_per_launch` for an NVLink-bound kernel")
+                         if (nvlink_measured or {}).get("tx_bytes_per_step_per_gpu") is not None else
+                         ("null: this box's NVML does not expose the NVLink throughput counters (%s); the single-collective "
+                          "timings of tools/nvls_probe.py stand in for them (DESIGN.md section 6)" % (nvlink_measured or {}).get("unavailable")),
                          "nvlink_measured": nvlink_measured,
                          "kernel": "mt_stream_kernel<DistAdamOp<mc_bf16,true>> (includes both barriers)",
                          "bytes_per_launch": nv_bytes, "avg_launch_ms": ms,
