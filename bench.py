@@ -395,6 +395,61 @@ def lamb_leg(mt, lib, dev, stream, peak, steps):
     }
 
 
+def sweep_leg(mt, lib, dev, stream, peak):
+    """configs[4]: the stress sweep T x n from 10,000 x 1K to 4 x 256M fp32 elements -- multi_tensor_scale, multi_tensor_l2norm,
+    multi_tensor_axpby -- one call at a time through the C ABI (descriptors built once), L2 flushed before each timed call,
+    median of 7; the 10,000-tensor end also through the Python entry points, with and without a prepared handle (host-bound)."""
+    import amp_C
+    flush = torch.empty(128 << 20, dtype=torch.float32, device=dev)
+    sp = stream.cuda_stream
+    flag = torch.zeros(1, dtype=torch.int32, device=dev)
+    fp = flag.data_ptr()
+    ret = torch.empty(1, device=dev)
+    rows = []
+
+    def cold(call, reps=7):
+        mt.check(call()); mt.check(call())
+        ts = []
+        for k in range(reps):
+            flush.fill_(float(k))
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream); mt.check(call()); e1.record(stream)
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1) * 1e3)
+        return statistics.median(ts)
+
+    for T, n in ((10000, 1024), (1000, 65536), (100, 1 << 20), (16, 1 << 26), (4, 1 << 28)):
+        x = torch.randn(T * n, device=dev)
+        y = torch.randn(T * n, device=dev)
+        o = torch.empty(T * n, device=dev)
+        xs, ys, os_ = (list(t.view(T, n).unbind(0)) for t in (x, y, o))
+        Lsc, Ln, Lax = mt.pack([xs, os_], 2), mt.pack([xs], 1), mt.pack([xs, ys, os_], 3)
+        for op, bpe, call in (("scale", 8.0, lambda: lib.b200mt_scale(Lsc.ref(), CHUNK, fp, 0.5, sp)),
+                              ("l2norm", 4.0, lambda: lib.b200mt_l2norm(Ln.ref(), CHUNK, fp, ret.data_ptr(), None, 0, sp)),
+                              ("axpby", 12.0, lambda: lib.b200mt_axpby(Lax.ref(), CHUNK, fp, 2.0, 0.5, -1, sp))):
+            us = cold(call)
+            rows.append({"shape": "%dx%d" % (T, n), "op": op, "us_per_call": round(us, 2), "gbs": round(bpe * T * n / us / 1e3, 1),
+                         "frac": round(bpe * T * n / us / 1e3 / peak, 3)})
+        if T == 10000:       # the host-bound end: wall time per call through amp_C.*, plain lists vs amp_C.prepare
+            hs = amp_C.prepare([xs, os_])
+            for name, call in (("amp_C.multi_tensor_scale(lists)", lambda: amp_C.multi_tensor_scale(CHUNK, flag, [xs, os_], 0.5)),
+                               ("amp_C.multi_tensor_scale(prepared)", lambda: amp_C.multi_tensor_scale(CHUNK, flag, hs, 0.5))):
+                for _ in range(3):
+                    call()
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                for _ in range(30):
+                    call()
+                torch.cuda.synchronize()
+                rows.append({"shape": "10000x1024", "op": name, "us_per_call": round((time.perf_counter() - t0) / 30 * 1e6, 1)})
+            hs.release()
+        del x, y, o, xs, ys, os_
+        torch.cuda.empty_cache()
+    assert int(flag) == 0
+    return {"workload": "configs[4]: stress sweep, fp32, chunk_size 65536", "rows": rows,
+            "timing": "CUDA events around ONE call (includes the launch latency of an idle stream, ~5 us), 512 MiB written before each"}
+
+
 def sharded_w1_leg(mt, lib, dev, stream, peak, steps):
     """configs[3] on ONE GPU: the shard-local kernel of DistributedFusedAdam (b200mt_dist_adam, [p32, m32, v32, g bf16,
     p_copy bf16], per-tensor hyper-parameters) over the WHOLE Llama-3-8B list -- the W = 1 point of the strong-scaling
@@ -678,6 +733,7 @@ def run_single(args):
     cold = None if skip_extra else cold_leg(mt, lib, dev, stream, L_scale, L_adam, fp, nparams, peak)
     # release the ResNet-50 e2e / mixed-precision buffers before the large legs
     lamb = None if skip_extra else lamb_leg(mt, lib, dev, stream, peak, args.steps)
+    sweep = None if skip_extra else sweep_leg(mt, lib, dev, stream, peak)
     w1 = None if (skip_extra or os.environ.get("B200MT_BENCH_SKIP_W1")) else sharded_w1_leg(mt, lib, dev, stream, peak, args.steps)
     if os.environ.get("B200MT_BENCH_SKIP_CPU"):   # profiling runs only: keep the command short under ncu
         cpu = {"value": None, "cores": 0, "steps": 0, "host_cpus": os.cpu_count(), "ms_per_step": None}
@@ -718,6 +774,7 @@ def run_single(args):
         "table_uploads": int(lib.b200mt_table_uploads()), "table_hits": int(lib.b200mt_table_hits()),
         "cold_cache": cold,
         "lamb_bert_large": lamb,
+        "stress_sweep": sweep,
         "sharded_w1": w1,
     }
     print(json.dumps(line))

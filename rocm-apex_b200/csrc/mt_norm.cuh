@@ -1,11 +1,12 @@
 // mt_norm.cuh -- second pass of the deterministic two-pass norm.
 //
 // Pass 1 (any streaming Op) leaves one fp32 partial sum of squares per tile in scratch.
-// Pass 2 (this kernel): one CTA per tensor adds the tile partials of each chunk in order, checks
-// every chunk sum for inf/NaN (the reference raises the noop flag per chunk,
-// csrc/multi_tensor_l2norm_kernel.cu:99-108), adds the chunk sums in a fixed thread-strided order
-// and a fixed shuffle tree, and writes sqrt(total) per tensor.  The CTA that finishes last sums the
-// per-tensor totals in index order for the global norm.  No float atomics anywhere, so results are
+// Pass 2 (norm_cleanup_kernel): per tensor, the tile partials of each chunk are added in order, every
+// chunk sum is checked for inf/NaN (the reference raises the noop flag per chunk,
+// csrc/multi_tensor_l2norm_kernel.cu:99-108), the chunk sums are added in a fixed thread-strided order
+// and a fixed shuffle tree, and sqrt(total) is written per tensor -- by one thread, one warp or one CTA
+// depending on the tensor's size, with identical arithmetic.  The CTA that finishes last (or the only
+// one) sums the per-tensor totals in index order for the global norm.  No float atomics anywhere, so results are
 // bitwise reproducible run to run.  Replaces cleanup / cleanup_v3 of the reference
 // (csrc/multi_tensor_l2norm_kernel.cu:198-237) and its 320-slot accumulate-across-launches scheme.
 #pragma once
