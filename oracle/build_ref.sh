@@ -13,7 +13,7 @@
 # (-O3 --use_fast_math -lineinfo + the VERSION_GE_* macros, setup.py:145-154) plus the four
 # -D__CUDA_NO_HALF*/BFLOAT16* defines torch's CUDAExtension adds to every nvcc line (without them
 # multi_tensor_distopt_lamb_kernel.cu:352 meets an ambiguous operator!= on at::Half).
-#   pyref/apex/**.py           <- the reference's Python package, staged unmodified (tests run it over both back ends)
+#   pyref.zip, pyref_tests.zip <- the reference's Python package and its unit tests for the path, as bytecode archives
 # Only tests/, __graft_entry__.smoke() and bench.py's comparison legs may load these.
 set -euo pipefail
 REF=${REF:-/root/reference}
@@ -76,18 +76,25 @@ build_module distributed_lamb_cuda_ref \
   $REF/apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb_kernel.cu
 rm -rf "$OBJ"
 
-# The reference's own Python (apex/**/*.py, unmodified, .py files only) staged next to the compiled checkers, so that
-# tests/test_reference_python_gpu.py can run the reference's optimizer / amp classes on the GPU box -- once over this
-# repo's amp_C shim and once over amp_C_ref -- and compare.  oracle/_ref/ is git-ignored: nothing of it enters the history.
-if [ ! -d "$OUT/pyref/apex" ] || [ -n "${FORCE:-}" ]; then
-  rm -rf "$OUT/pyref"
-  mkdir -p "$OUT/pyref"
+# The reference's own Python for this path, staged next to the compiled checkers AS BYTECODE ONLY (python -m compileall -b, the
+# .py files are deleted again): like the .so files it is a build product of the reference, importable but not source, so that
+# tests/test_reference_python_gpu.py and tests/test_reference_suite_gpu.py can run the reference's optimizer / amp classes and
+# its own unit tests on the GPU box -- once over this repo's amp_C shim and once over amp_C_ref -- and compare.
+# oracle/_ref/ is git-ignored: nothing of it enters the history.
+if [ ! -f "$OUT/pyref.zip" ] || [ ! -f "$OUT/pyref_tests.zip" ] || [ -n "${FORCE:-}" ]; then
+  rm -rf "$OUT/pyref" "$OUT/pyref_tests" "$OUT/pyref.zip" "$OUT/pyref_tests.zip"
+  mkdir -p "$OUT/pyref" "$OUT/pyref_tests"
   (cd "$REF" && find apex -name '*.py' | while read -r f; do mkdir -p "$OUT/pyref/$(dirname "$f")"; cp "$f" "$OUT/pyref/$f"; done)
-  # ... and the reference's own unit tests for this path (tests/L0/run_amp, tests/L0/run_optimizers), to be run over both back ends
-  mkdir -p "$OUT/pyref_tests"
   for d in run_amp run_optimizers; do
     mkdir -p "$OUT/pyref_tests/$d"
     cp "$REF"/tests/L0/$d/*.py "$OUT/pyref_tests/$d/"
   done
-  echo "[oracle/build_ref] staged $(find "$OUT/pyref" -name '*.py' | wc -l) reference .py files under $OUT/pyref"
+  $PY -W ignore -m compileall -q -b "$OUT/pyref" "$OUT/pyref_tests" > /dev/null 2>&1 || true   # files that do not compile under this Python are not on the path
+  find "$OUT/pyref" "$OUT/pyref_tests" -name '*.py' -delete
+  n=$(find "$OUT/pyref" "$OUT/pyref_tests" -name '*.pyc' | wc -l)
+  # one importable archive each (zipimport reads sourceless .pyc): a single binary file travels with gpurun like the .so files
+  (cd "$OUT/pyref" && $PY -m zipfile -c "$OUT/pyref.zip" apex)
+  (cd "$OUT/pyref_tests" && $PY -m zipfile -c "$OUT/pyref_tests.zip" run_amp run_optimizers)
+  rm -rf "$OUT/pyref" "$OUT/pyref_tests"
+  echo "[oracle/build_ref] staged $n reference modules as bytecode in $OUT/pyref.zip, $OUT/pyref_tests.zip"
 fi

@@ -1,5 +1,5 @@
-"""Subprocess body of tests/test_reference_python_gpu.py: runs the REFERENCE's own Python (oracle/_ref/pyref/apex, the
-unmodified package staged by oracle/build_ref.sh) over one of two back ends and saves what it computed.
+"""Subprocess body of tests/test_reference_python_gpu.py: runs the REFERENCE's own Python (oracle/_ref/pyref.zip: the
+unmodified package, compiled to bytecode and archived by oracle/build_ref.sh) over one of two back ends and saves what it computed.
 
   python tests/_refpy_worker.py ours <out.pt>    amp_C = this repo's shim over libb200mt.so (rocm-apex_b200/amp_C.py)
   python tests/_refpy_worker.py ref  <out.pt>    amp_C = oracle/_ref/amp_C_ref.so, the reference's own kernels
@@ -14,7 +14,7 @@ import sys
 import types
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-PYREF = os.path.join(ROOT, "oracle", "_ref", "pyref")
+PYREF = os.path.join(ROOT, "oracle", "_ref", "pyref.zip")      # bytecode archive of the reference's apex package
 
 
 def setup(backend):

@@ -1,12 +1,13 @@
 """Subprocess body of tests/test_reference_suite_gpu.py: runs the REFERENCE's own unit tests for the hot path
-(/root/reference/tests/L0/run_amp and run_optimizers, staged unmodified under oracle/_ref/pyref_tests by
-oracle/build_ref.sh) with the reference's own Python package (oracle/_ref/pyref) over one of two back ends:
+(/root/reference/tests/L0/run_amp and run_optimizers, staged unmodified, as a bytecode archive, in oracle/_ref/pyref_tests.zip by
+oracle/build_ref.sh) with the reference's own Python package (oracle/_ref/pyref.zip) over one of two back ends:
 
   python tests/_reftests_runner.py ours <out.json> <dir/test_file.py> ...   amp_C = this repo's shim over libb200mt.so
   python tests/_reftests_runner.py ref  <out.json> <dir/test_file.py> ...   amp_C = the reference's kernels (amp_C_ref.so)
 
 Writes {test id: "ok" | "fail: ..." | "error: ..." | "skip: ..."} as JSON.
 """
+import importlib
 import json
 import os
 import sys
@@ -15,7 +16,7 @@ import unittest
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 from _refpy_worker import ROOT, setup   # noqa: E402
 
-TESTS = os.path.join(ROOT, "oracle", "_ref", "pyref_tests")
+TESTS = os.path.join(ROOT, "oracle", "_ref", "pyref_tests.zip")
 
 
 class Result(unittest.TextTestResult):
@@ -43,7 +44,11 @@ def main():
     for rel in files:
         d, f = os.path.split(rel)
         sys.path.insert(0, os.path.join(TESTS, d))          # the tests do `from utils import common_init`
-        suite = unittest.defaultTestLoader.discover(os.path.join(TESTS, d), pattern=f, top_level_dir=os.path.join(TESTS, d))
+        # the staged tests are a bytecode archive (oracle/build_ref.sh): import the module through zipimport
+        name = os.path.splitext(f)[0]
+        sys.modules.pop("utils", None)                        # each test directory has its own utils module
+        mod = importlib.import_module(name)
+        suite = unittest.defaultTestLoader.loadTestsFromModule(mod)
         runner = unittest.TextTestRunner(resultclass=Result, verbosity=1, stream=sys.stderr)
         r = runner.run(suite)
         outcomes.update(r.outcomes)

@@ -20,7 +20,7 @@ WORKER = os.path.join(ROOT, "tests", "_refpy_worker.py")
 
 @pytest.fixture(scope="module")
 def runs(tmp_path_factory):
-    if not os.path.isdir(os.path.join(ROOT, "oracle", "_ref", "pyref", "apex")):
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "pyref.zip")):
         pytest.skip("oracle/_ref/pyref not staged (oracle/build_ref.sh)")
     if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "amp_C_ref.so")):
         pytest.skip("oracle/_ref/amp_C_ref.so not built")
