@@ -129,6 +129,14 @@ def gpu_numa_cpus(dev_index):
         return None
 
 
+def host_numa_nodes():
+    """Number of NUMA nodes the host shows (1 on the single-node VMs of this pool: placement is then moot)."""
+    try:
+        return len([d for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()])
+    except Exception:
+        return None
+
+
 def pinned_near_gpu(numel, dtype, dev_index):
     """Pinned host tensor whose pages sit on the GPU's own NUMA node: allocated and first touched while this thread
     is confined to that node's CPUs (H2D from the far socket runs at ~30 GB/s instead of ~55 on these boxes); the

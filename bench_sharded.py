@@ -21,10 +21,10 @@ NVLINK_GBS = 770.0     # measured peer-copy bandwidth per direction (B200_PROFIL
 
 def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, stream, flat, nparams, shapes, model_name, lib,
                   parity=None, parity_ok=True, nvlink_measured=None):
-    from bench import peaks, pinned_near_gpu, gpu_numa_cpus, METRIC, UNIT
+    from bench import peaks, pinned_near_gpu, gpu_numa_cpus, host_numa_nodes, METRIC, UNIT
     clocks = sampler.stop() if rank == 0 else None
     host = pinned_near_gpu(1 << 27, torch.bfloat16, local)
-    numa_known = gpu_numa_cpus(local) is not None
+    numa_known = gpu_numa_cpus(local) is not None or host_numa_nodes() == 1
     host.normal_(0, 1)
     e2e_steps = max(2, min(args.steps, 5))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -85,7 +85,10 @@ def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, str
                          "hbm_gbs_of_shard_kernel": achieved, "hbm_frac": achieved / peak},
             "cpu_baseline": None,
             "e2e": {"value": nparams / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 2 * total * world, "d2h_bytes_per_step": 2 * world,
-                    "ms_per_step": e2e_ms, "steps": e2e_steps, "pinned_on_gpu_numa_node": numa_known,
+                    "ms_per_step": e2e_ms, "steps": e2e_steps, "pinned_on_gpu_numa_node": numa_known, "host_numa_nodes": host_numa_nodes(),
+                    "note": "every rank copies its whole 2-byte gradient buffer from host memory each step (data-parallel ranks all hold full "
+                            "gradients): N x 16 GB per step over N PCIe links out of ONE host memory system, so this number is paced by "
+                            "PCIe and host DRAM, not by the optimizer",
                     "api": "DistributedFusedAdam(fused_collectives=True).complete_reductions() + step(), grads copied from pinned host each step"},
             "gpu_launches": int(tl.item()),
             "clocks": clocks,
@@ -268,9 +271,9 @@ def run_sharded(args):
 
     # e2e: the step's gradients arrive from pinned host memory (a 256 MiB pinned window copied repeatedly to
     # fill the flat buffer: pinning 16 GB per rank is not reasonable), the result read back is the gradient norm
-    from bench import pinned_near_gpu, gpu_numa_cpus
+    from bench import pinned_near_gpu, gpu_numa_cpus, host_numa_nodes
     host = pinned_near_gpu(1 << 27, torch.bfloat16, local)
-    numa_known = gpu_numa_cpus(local) is not None
+    numa_known = gpu_numa_cpus(local) is not None or host_numa_nodes() == 1
     host.normal_(0, 1)
     e2e_steps = max(2, min(args.steps, 5))
 

@@ -244,11 +244,11 @@ int b200mt_maybe_adam_undo(const b200mt_lists* lists, int chunk_size, const int3
 
 /* ---- prepared list sets -- no counterpart in the reference, whose harness re-packs the tensor addresses into kernel
  * arguments on every call (csrc/multi_tensor_apply.cuh:84-146: the cost this removes).
- * By default every entry point rebuilds the descriptor-table image of its list set, hashes it and compares it with the
- * cached copy: O(depth * ntensors) host work per call, which for lists of thousands of small tensors is longer than the
+ * By default every entry point rebuilds the descriptor-table image of its list set, compares it with the
+ * cached copies: O(depth * ntensors) host work per call, which for lists of thousands of small tensors is longer than the
  * kernel.  A host that KNOWS its tensors stay where they are (optimizer state, flat gradient views, bucket buffers)
  * can prepare the list set once and pass the handle in lists->prepared on every call: the library then uses the
- * handle's resident table directly -- no image, no hash, no compare.  ptrs / numel / ntensors / depth / dtype / device
+ * handle's resident table directly -- no image, no compare.  ptrs / numel / ntensors / depth / dtype / device
  * must still describe the same list set (ntensors, depth and device are checked against the handle; the pointers are
  * NOT re-read: moving a tensor without preparing again is the caller's bug).  One handle serves every op: the table
  * for a kind of op (element-wise, norm-type per chunk size) is uploaded on the handle's first use with it, on that

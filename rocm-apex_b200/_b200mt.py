@@ -181,7 +181,7 @@ class Packed(object):
 
 class Prepared(Packed):
     """A list set prepared once (b200mt_lists_prepare): every drop-in entry point accepts it in place of
-    `tensor_lists` and then skips the per-call walk of the lists, the table image, its hash and the compare -- what
+    `tensor_lists` and then skips the per-call walk of the lists, the table image and the compare -- what
     is left of a call is the launch.  The caller promises that the tensors stay at their addresses and sizes for the
     life of the object (it keeps the tensor objects alive, so freed storage cannot be reused under it; re-pointing a
     tensor with `.data =` / `set_()` / `resize_()` is the one thing that breaks the promise).  release() or garbage

@@ -53,3 +53,16 @@ def test_amp_c_module_has_reference_entry_points():
                  "multi_tensor_lamb_mp", "multi_tensor_lamb_stage1_cuda", "multi_tensor_lamb_stage2_cuda",
                  "multi_tensor_adagrad", "multi_tensor_novograd"):
         assert callable(getattr(amp_C, name))
+
+
+def test_plain_c_host_compiles_links_and_gets_errors(tmp_path):
+    """tests/cabi/host.c: a host in plain C99 (-Wall -Wextra -Werror -pedantic) includes the header, links the library
+    and exercises argument checking -- no GPU involved."""
+    import subprocess
+    libdir = os.path.join(ROOT, "rocm-apex_b200")
+    exe = str(tmp_path / "cabi_host")
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "cabi", "host.c"), "-o", exe, "-L", libdir, "-lb200mt",
+                           "-Wl,-rpath," + libdir])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout + r.stderr

@@ -1,7 +1,7 @@
 """GPU: prepared list sets (b200mt_lists_prepare / amp_C.prepare) and the launch trace (b200mt_trace_begin / _end).
 
 A prepared handle must give exactly the results of the plain call -- it only skips the per-call host work (list walk,
-table image, hash, compare) -- for every kind of op it is used with (element-wise and norm-type tables are created on
+table image, compare) -- for every kind of op it is used with (element-wise and norm-type tables are created on
 first use), on several streams, inside a CUDA graph after a warm-up, and must refuse list sets it was not made for.
 """
 import ctypes
@@ -113,7 +113,7 @@ def test_prepared_on_two_streams_and_in_a_graph():
 
 def test_prepared_removes_the_per_call_host_work_on_10000_tensors():
     """10,000 x 1,024-element tensors (BASELINE.json configs[4], small end): the plain call walks 20,000 tensors and
-    hashes a 240 KB image per call; the prepared call must cost a small fraction of that on the host."""
+    builds and compares a 240 KB image per call; the prepared call must cost a small fraction of that on the host."""
     import amp_C
     big = torch.randn(10000 * 1024, device="cuda")
     out = torch.empty_like(big)

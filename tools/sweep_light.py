@@ -131,7 +131,7 @@ for name, call in (("scale", lambda: amp_C.multi_tensor_scale(CHUNK, f, [xs, os_
         call()
     torch.cuda.synchronize()
     r["10kx1K_%s_us_per_call" % name] = round((time.perf_counter() - t0) / 50 * 1e6, 1)
-# ... and with prepared list handles (amp_C.prepare): no walk, no image, no hash -- what is left is the launch
+# ... and with prepared list handles (amp_C.prepare): no walk, no image, no compare -- what is left is the launch
 hs, hn, ha = amp_C.prepare([xs, os_]), amp_C.prepare([xs]), amp_C.prepare([xs, ys, os_])
 for name, call in (("scale", lambda: amp_C.multi_tensor_scale(CHUNK, f, hs, 0.5)),
                    ("l2norm", lambda: amp_C.multi_tensor_l2norm(CHUNK, f, hn, False)),
