@@ -244,7 +244,7 @@ int b200mt_maybe_adam_undo(const b200mt_lists* lists, int chunk_size, const int3
 
 /* ---- prepared list sets -- no counterpart in the reference, whose harness re-packs the tensor addresses into kernel
  * arguments on every call (csrc/multi_tensor_apply.cuh:84-146: the cost this removes).
- * By default every entry point rebuilds the descriptor-table image of its list set, compares it with the
+ * By default every entry point rebuilds the descriptor-table image of its list set and compares it with the
  * cached copies: O(depth * ntensors) host work per call, which for lists of thousands of small tensors is longer than the
  * kernel.  A host that KNOWS its tensors stay where they are (optimizer state, flat gradient views, bucket buffers)
  * can prepare the list set once and pass the handle in lists->prepared on every call: the library then uses the

@@ -89,7 +89,7 @@ class FusedSGD(torch.optim.Optimizer):
             moms, first = self.get_momentums(ps)
             all_warm = all_warm and not (first and ps)
             sets.append(([[p.grad for p in ps], ps, moms], first))
-            rows_by_dt.append(([(p, self.state[p], m) for p, m in zip(ps, moms)], ps, moms))
+            rows_by_dt.append(([(p, self.state[p], m, m) for p, m in zip(ps, moms)], ps, moms, {}))
         if all_warm:
             idle = [p for p in group["params"] if p.grad is None]
             self._sets[gid] = (self.state, group["params"], len(group["params"]), idle, rows_by_dt)
@@ -99,19 +99,48 @@ class FusedSGD(torch.optim.Optimizer):
 
     @staticmethod
     def _memoised_sets(c):
+        """The cached [g, p, momentum] sets of one group, each as a prepared list handle when its gradients still sit
+        where they sat last step (one native loop checks addresses and the identity of the momentum buffers; see
+        _common.GroupCache.launch_sets), else as plain lists."""
+        import _b200mt as mt
         for p in c[3]:
             if p.grad is not None:
                 return None
         sets = []
-        for rows, ps, moms in c[4]:
+        for rows, ps, moms, h in c[4]:
+            if not rows:
+                sets.append(([[], ps, moms], False))
+                continue
+            if mt.check_rows is not None and h.get("prep") is not None:
+                rc = mt.check_rows(rows, "momentum_buffer", "momentum_buffer", h["prep"].ptrs.ctypes.data, h["code"])
+                if rc == 0:
+                    h["misses"] = 0
+                    sets.append((h["prep"], False))
+                    continue
+                if rc == 2:
+                    return None
             gs = []
             add = gs.append
-            for p, st, mom in rows:
+            for p, st, mom, _ in rows:
                 g = p.grad
                 if g is None or st.get("momentum_buffer") is not mom:
                     return None
                 add(g)
-            sets.append(([gs, ps, moms], False))
+            lists = [gs, ps, moms]
+            if mt.check_rows is not None:
+                if h.get("prep") is not None:
+                    h["prep"].release()
+                    h["prep"] = None
+                    h["misses"] = h.get("misses", 0) + 1
+                if h.get("misses", 0) < 3 and not any(g.is_sparse for g in gs):
+                    try:
+                        h["prep"] = mt.prepare(lists, keep=False)     # gradient addresses are re-checked before every use
+                        h["code"] = mt.dtype_code(gs[0])
+                        sets.append((h["prep"], False))
+                        continue
+                    except RuntimeError:
+                        pass                                          # the plain call reports what is wrong with the lists
+            sets.append((lists, False))
         return sets
 
     @torch.no_grad()
@@ -119,9 +148,10 @@ class FusedSGD(torch.optim.Optimizer):
         loss = closure() if closure is not None else None
         for gid, group in enumerate(self.param_groups):
             for lists, first_run in self._launch_sets(gid, group):
-                assert len(lists[0]) == len(lists[1]) == len(lists[2])
-                if len(lists[0]) == 0:
-                    continue
+                if not hasattr(lists, "handle"):                      # plain lists (a prepared handle was validated when made)
+                    assert len(lists[0]) == len(lists[1]) == len(lists[2])
+                    if len(lists[0]) == 0:
+                        continue
                 multi_tensor_applier(self.multi_tensor_sgd, self._dummy_overflow_buf, lists,
                                      group["weight_decay"], group["momentum"], group["dampening"], group["lr"],
                                      group["nesterov"], first_run, self.wd_after_momentum,

@@ -190,3 +190,42 @@ def test_fused_adam_prepared_handle_follows_the_gradients():
         p.grad = torch.randn(p.shape, generator=g, device="cuda"); q.grad = p.grad.clone()
     fx.step(); ty.step()
     assert same(x[1:], y[1:], tol=1e-5)
+
+
+def test_fused_sgd_prepared_handle_follows_the_gradients():
+    """FusedSGD's memoised [g, p, momentum] sets go to the kernel as a prepared handle while the gradients stay put, are
+    re-prepared when they move and fall back to plain lists when they keep moving; next to torch.optim.SGD throughout."""
+    import _b200mt as mt
+    from apex.optimizers import FusedSGD
+    if mt.check_rows is None:
+        pytest.skip("native packer not built")
+    kw = dict(lr=0.05, momentum=0.9, weight_decay=0.01, nesterov=True)
+    x, y = make(seed=4)
+    fx, ty = FusedSGD(x, **kw), torch.optim.SGD(y, **kw)
+    g = torch.Generator(device="cuda").manual_seed(6)
+    for p, q in zip(x, y):
+        p.grad = torch.randn(p.shape, generator=g, device="cuda"); q.grad = p.grad.clone()
+    for it in range(2):                                   # step 0 creates the momentum buffers, step 1 builds the memo
+        fx.step(); ty.step()
+    handle = lambda: fx._sets[0][4][1][3].get("prep")    # the fp32 bucket
+    hits0 = None
+    for it in range(4):
+        for p, q in zip(x, y):
+            p.grad.copy_(torch.randn(p.shape, generator=g, device="cuda")); q.grad.copy_(p.grad)
+        fx.step(); ty.step()
+        assert same(x, y, tol=1e-5)
+        assert handle() is not None
+        if hits0 is None:
+            first, hits0 = handle(), mt.lib.b200mt_table_hits()
+    assert handle() is first and mt.lib.b200mt_table_hits() >= hits0 + 3
+    keep = []
+    for it in range(5):                                   # gradients somewhere else every step
+        for p, q in zip(x, y):
+            p.grad = torch.randn(p.shape, generator=g, device="cuda"); q.grad = p.grad.clone()
+            keep.append(p.grad)
+        fx.step(); ty.step()
+        assert same(x, y, tol=1e-5)
+    assert handle() is None
+    fx.state[x[3]]["momentum_buffer"] = fx.state[x[3]]["momentum_buffer"].clone()      # state replaced: memo rebuilt
+    fx.step(); ty.step()
+    assert same(x, y, tol=1e-5)
