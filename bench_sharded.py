@@ -57,16 +57,24 @@ def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, str
         # per GPU and direction: out = my whole gradient buffer pulled by the switch (2*total) + my shard's
         # parameters sent once (2*shard); in = my shard's reduced gradients (2*shard) + everybody's parameters (2*total)
         pbytes = 1.0 if opt._e5m2 else 2.0     # bytes per parameter in the broadcast
-        nv_bytes = 2.0 * total + pbytes * shard_elems          # the busier (outgoing) direction
+        p2p = getattr(opt, "_fused_form", None) == "p2p"
+        if p2p:     # two ranks over peer memory: the peer reads my copy of its shard (2*shard out), I write my shard's parameters to it
+            nv_bytes = 2.0 * shard_elems + pbytes * shard_elems
+        else:
+            nv_bytes = 2.0 * total + pbytes * shard_elems      # the busier (outgoing) direction
         kbytes = (26.0 + pbytes) * shard_elems
         achieved = kbytes / (ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": nparams / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "configs[3]: DistributedFusedAdam sharded step on the %s shape list as ONE kernel over NVSwitch multicast: "
-                                   "bf16 grads reduced in the switch on load (multimem.ld_reduce), fused AdamW (fp32 master/moments), "
-                                   "bf16 params broadcast by the switch on store (multimem.st)" % model_name,
+            "config": {"workload": ("configs[3]: DistributedFusedAdam sharded step on the %s shape list as ONE kernel over peer-mapped memory "
+                                    "(two ranks): the peer's bf16 grads added on load, fused AdamW (fp32 master/moments), bf16 params stored "
+                                    "here and in the peer" % model_name) if p2p else
+                                   ("configs[3]: DistributedFusedAdam sharded step on the %s shape list as ONE kernel over NVSwitch multicast: "
+                                    "bf16 grads reduced in the switch on load (multimem.ld_reduce), fused AdamW (fp32 master/moments), "
+                                    "bf16 params broadcast by the switch on store (multimem.st)" % model_name),
+                       "fused_form": getattr(opt, "_fused_form", None),
                        "tensors": len(shapes), "params": nparams, "flat_elems": total, "parallelism": "zero-dp%d" % world,
                        "e5m2_allgather": bool(opt._e5m2),
                        "l2": "inputs larger than L2 (%.1f GB of optimizer state per rank)" % (12.0 * shard_elems / 1e9)},
@@ -79,7 +87,8 @@ def _report_fused(args, opt, ms, launches, sampler, rank, world, local, dev, str
                          ("null: this box's NVML does not expose the NVLink throughput counters (%s); the single-collective "
                           "timings of tools/nvls_probe.py stand in for them (DESIGN.md section 6)" % (nvlink_measured or {}).get("unavailable")),
                          "nvlink_measured": nvlink_measured,
-                         "kernel": "mt_stream_kernel<DistAdamOp<mc_bf16,true>> (includes both barriers)",
+                         "kernel": ("mt_stream_kernel<DistAdamOp<pair_bf16,pair_bf16,true>>" if p2p else
+                                    "mt_stream_kernel<DistAdamOp<mc_bf16,mc_bf16,true>>") + " (includes both barriers)",
                          "bytes_per_launch": nv_bytes, "avg_launch_ms": ms,
                          "peak_source": "measured peer-copy bandwidth per direction (B200_PROFILING.md), 900 nominal",
                          "hbm_gbs_of_shard_kernel": achieved, "hbm_frac": achieved / peak},
@@ -133,7 +142,8 @@ def run_sharded(args):
             params.append(torch.nn.Parameter((torch.randn(s, generator=gen, device=dev, dtype=torch.float32) * 0.02).to(torch.bfloat16)))
         o = DistributedFusedAdam(params, lr=1e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1, dwu_num_blocks=chunks,
                                  dwu_num_chunks=1, predivide=False, overlap_reductions=False, zero_copy_params=not e5m2,
-                                 fused_collectives=fused_flag, e5m2_allgather=e5m2)
+                                 fused_collectives=((os.environ.get("B200MT_SHARDED_FORM") or True) if fused_flag else False),
+                                 e5m2_allgather=e5m2)
         o.set_global_scale(float(world))        # gradients are summed by the reduce-scatter; the kernel divides by W
         fl = o.attach_flat_grads()
         ggen = torch.Generator(device=dev).manual_seed(100 + rank)

@@ -205,6 +205,21 @@ int b200mt_dist_adam_nvls(const b200mt_lists* lists, int chunk_size, int32_t* no
                           const float* per_tensor_weight_decay, float lr, float grad_scale, int step,
                           int mode, void* stream);
 
+/* ---- b200mt_dist_adam_p2p -- the same sharded step for TWO ranks over peer-mapped memory (extension, no reference
+ * counterpart beyond the three-step sequence above).  lists = [p32, m32, v32, g, p_copy]: g and p_copy are this rank's
+ * addresses (BFloat16) inside buffers that have a twin in the peer GPU's memory, mapped into this process at
+ * `grad_peer_delta` / `copy_peer_delta` bytes from them (symmetric memory: peer base - own base).  The gradient load adds
+ * the peer's value (fp32 sum, one rounding to bf16: the two-rank reduce-scatter), the parameter store also writes the
+ * peer's twin (the two-rank all-gather).  Per direction 4 bytes per shard element cross the link; the multicast kernel
+ * needs 6 at W = 2 because the switch pulls the requester's own half through the links too.  Fragments: multiples of 8
+ * elements, 16-byte aligned (fp32 lists 32-byte).  Barriers around the launch as for b200mt_dist_adam_nvls.  The distances
+ * are written to constant memory on `stream` before the launch: concurrent launches with DIFFERENT distances must share a stream. */
+int b200mt_dist_adam_p2p(const b200mt_lists* lists, int chunk_size, int32_t* noop,
+                         const float* per_tensor_beta1, const float* per_tensor_beta2,
+                         const int32_t* per_tensor_bias_correction, const float* per_tensor_eps,
+                         const float* per_tensor_weight_decay, float lr, float grad_scale, int step,
+                         int mode, int64_t grad_peer_delta, int64_t copy_peer_delta, void* stream);
+
 /* ---- b200mt_nvls_reduce_scatter / b200mt_nvls_all_gather -- the two collectives of the sharded step
  * (torch.distributed.reduce_scatter / all_gather at apex/contrib/optimizers/distributed_fused_adam.py:409,477)
  * as stand-alone kernels over NVSwitch multicast memory, for callers that want them unfused.

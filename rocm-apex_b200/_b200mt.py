@@ -80,6 +80,8 @@ def _load():
         "b200mt_lamb_stage2": (c_int, [LP, c_int, vp, vp, vp, c_float, c_float, c_int, vp]),
         "b200mt_dist_adam": (c_int, [LP, c_int, vp, vp, vp, vp, vp, vp, c_float, c_float, c_int, c_int, vp]),
         "b200mt_dist_adam_nvls": (c_int, [LP, c_int, vp, vp, vp, vp, vp, vp, c_float, c_float, c_int, c_int, vp]),
+        "b200mt_dist_adam_p2p": (c_int, [LP, c_int, vp, vp, vp, vp, vp, vp, c_float, c_float, c_int, c_int, ctypes.c_int64,
+                                         ctypes.c_int64, vp]),
         "b200mt_adagrad": (c_int, [LP, c_int, vp, c_float, c_float, c_int, c_float, vp]),
         "b200mt_novograd": (c_int, [LP, c_int, vp, vp, c_float, c_float, c_float, c_float, c_int, c_int, c_float, c_int,
                                     c_int, c_int, vp]),

@@ -126,7 +126,14 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         # gradients are summed over the ranks inside the switch while they are loaded (multimem.ld_reduce) and
         # the updated low-precision parameters are replicated to every rank by the switch as they are stored
         # (multimem.st).  No reduce_scatter, no all_gather, no pipeline chunks; two cross-GPU barriers per step.
-        self._fused = fused_collectives
+        # True picks the form by world size: with TWO ranks the kernel reads the peer's gradients and writes the peer's
+        # parameters directly through peer-mapped memory ("p2p": 4 bytes per shard element and direction on the link,
+        # where the multicast form moves 6 because the switch pulls the requester's own half too); from three ranks on the
+        # in-switch reduction wins ("multimem").  Either name forces that form.
+        if fused_collectives not in (False, True, "multimem", "p2p"):
+            raise ValueError("fused_collectives must be False, True, 'multimem' or 'p2p'")
+        self._fused = bool(fused_collectives)
+        self._fused_form = fused_collectives if isinstance(fused_collectives, str) else None
         # zero_copy_params (not in the reference): re-point every model parameter's storage at its slot of
         # the all-gather output buffer, so the gathered parameters ARE the model parameters and the final
         # scatter-back pass (maybe_cast_mt, 4 B/param of HBM traffic) disappears.
@@ -237,7 +244,16 @@ class DistributedFusedAdam(torch.optim.Optimizer):
             self._flat_grads.zero_(); self._new_params.zero_()
             self._hdl_g = symm_mem.rendezvous(self._flat_grads, self._pg.group_name)
             self._hdl_p = symm_mem.rendezvous(self._new_params, self._pg.group_name)
-            if not (self._hdl_g.multicast_ptr and self._hdl_p.multicast_ptr):
+            if self._fused_form is None:
+                self._fused_form = "p2p" if (W == 2 and not self._e5m2 and low == torch.bfloat16) else "multimem"
+            if self._fused_form == "p2p":
+                if W != 2 or self._e5m2 or low != torch.bfloat16:
+                    raise ValueError("fused_collectives='p2p' is the two-rank bf16 form")
+                peer = 1 - r
+                # byte distance from this rank's buffer to the peer's copy of it, both mapped into this process
+                self._p2p_delta = (int(self._hdl_g.buffer_ptrs[peer]) - int(self._hdl_g.buffer_ptrs[r]),
+                                   int(self._hdl_p.buffer_ptrs[peer]) - int(self._hdl_p.buffer_ptrs[r]))
+            elif not (self._hdl_g.multicast_ptr and self._hdl_p.multicast_ptr):
                 raise RuntimeError("fused_collectives: no multicast (NVLS) address for the symmetric buffers; "
                                    "this needs an NVSwitch domain with multicast support")
         else:
@@ -271,9 +287,13 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                     esize = self._flat_grads.element_size()
                     for lst, buf in zip(lists[:3], (self._fp32_p, self._fp32_m, self._fp32_v)):
                         lst.append(buf[base + soff:base + soff + n])
-                    lists[3].append(RawBuffer(self._hdl_g.multicast_ptr + flat_pos * esize, n, low, dev))
-                    lists[4].append(RawBuffer(self._hdl_p.multicast_ptr + flat_pos * self._new_params.element_size(),
-                                              n, gathered, dev))
+                    if self._fused_form == "p2p":      # this rank's own views; the kernel adds the distance to the peer's copies
+                        lists[3].append(self._flat_grads[flat_pos:flat_pos + n])
+                        lists[4].append(self._new_params[flat_pos:flat_pos + n])
+                    else:
+                        lists[3].append(RawBuffer(self._hdl_g.multicast_ptr + flat_pos * esize, n, low, dev))
+                        lists[4].append(RawBuffer(self._hdl_p.multicast_ptr + flat_pos * self._new_params.element_size(),
+                                                  n, gathered, dev))
                 else:
                     sl = slice(base + soff, base + soff + n)
                     for lst, buf in zip(lists, (self._fp32_p, self._fp32_m, self._fp32_v, self._fp16_g, self._fp16_p)):
@@ -486,6 +506,10 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         if len(lists[0]) == 0:
             return
         b1, b2, bc, ep, wd = self._chunk_hyper[k]
+        if self._fused and self._fused_form == "p2p":
+            multi_tensor_applier(self._dist_adam.multi_tensor_fused_adam_p2p, self._overflow_buf, lists, b1, b2, bc, ep, wd,
+                                 self.param_groups[0]["lr"], combined_scale, self._step, self.eps_mode, *self._p2p_delta)
+            return
         op = self._dist_adam.multi_tensor_fused_adam_nvls if self._fused else self._dist_adam.multi_tensor_fused_adam
         multi_tensor_applier(op, self._overflow_buf, lists, b1, b2, bc, ep, wd,
                              self.param_groups[0]["lr"], combined_scale, self._step, self.eps_mode)

@@ -402,6 +402,52 @@ template <> struct Elem<mc_f16> {
   static __device__ __forceinline__ float round_trip(float v) { return __half2float(__float2half_rn(v)); }
 };
 
+// Two-GPU peer view of a 16-bit list (b200mt_dist_adam_p2p): the pointer addresses THIS GPU's copy of a buffer that has a
+// twin at a fixed byte distance in the peer GPU's memory (both mapped into this process: symmetric memory).
+//   ld = this GPU's value + the peer's value, summed in fp32 and rounded once to the list's type -- the reduce-scatter of
+//        two ranks done by the load (what NCCL would hand over, without the trip through a reduced buffer);
+//   st = the value stored here AND in the peer's twin -- the all-gather of two ranks done by the store.
+// With two ranks this moves 2 bytes per element per direction for each collective; the multicast path moves
+// 2*(1 + 1/W) = 3: the switch pulls the requester's own half through the links as well.
+// The distances live in constant memory, written on the launching stream before the launch (b200mt_dist_adam_p2p).
+struct pair_bf16 {};
+__constant__ long long c_pair_delta[2];   // [0]: loads (gradients), [1]: stores (parameter copy); bytes to the peer's twin
+
+__device__ __forceinline__ uint4 ld_u4_sys(const void* p) {
+  uint4 r;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void st_u4_sys(void* p, uint4 v) {
+  asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+template <> struct Elem<pair_bf16> {
+  static constexpr int SIZE = 2, QUAD_ALIGN = 8;
+  static __device__ __forceinline__ void ld8(const void* p, float (&r)[8]) {
+    const uint4 a = ld_u4(p);
+    const uint4 b = ld_u4_sys(reinterpret_cast<const char*>(p) + c_pair_delta[0]);
+    float x[8], y[8];
+    bf16x2_to_f(a.x, x[0], x[1]); bf16x2_to_f(a.y, x[2], x[3]); bf16x2_to_f(a.z, x[4], x[5]); bf16x2_to_f(a.w, x[6], x[7]);
+    bf16x2_to_f(b.x, y[0], y[1]); bf16x2_to_f(b.y, y[2], y[3]); bf16x2_to_f(b.z, y[4], y[5]); bf16x2_to_f(b.w, y[6], y[7]);
+#pragma unroll
+    for (int i = 0; i < 8; i++) r[i] = __bfloat162float(__float2bfloat16_rn(x[i] + y[i]));
+  }
+  static __device__ __forceinline__ void st8(void* p, const float (&r)[8]) {
+    const uint4 v = make_uint4(f_to_bf16x2(r[0], r[1]), f_to_bf16x2(r[2], r[3]), f_to_bf16x2(r[4], r[5]), f_to_bf16x2(r[6], r[7]));
+    st_u4(p, v);
+    st_u4_sys(reinterpret_cast<char*>(p) + c_pair_delta[1], v);
+  }
+  // only whole 16-byte vectors exist on this path (the host entry point enforces it)
+  static __device__ __forceinline__ void ld4(const void*, float (&)[4]) { __trap(); }
+  static __device__ __forceinline__ void st4(void*, const float (&)[4]) { __trap(); }
+  static __device__ __forceinline__ float ld1(const void*) { __trap(); return 0.f; }
+  static __device__ __forceinline__ void st1(void*, float) { __trap(); }
+  static __device__ __forceinline__ float round_trip(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+};
+
 // Store-only multicast view of an e5m2 byte list (the compressed all-gather of the sharded Adam):
 // 4 or 8 packed bytes per multimem.st, replicated by the switch.
 struct mc_e5m2 {};

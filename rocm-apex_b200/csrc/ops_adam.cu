@@ -35,6 +35,7 @@ int adam_tma_launch(const TableView& tv, float beta1, float beta2, float bc1, fl
 template <typename T> struct is_mc { static constexpr bool value = false; };
 template <> struct is_mc<mc_bf16> { static constexpr bool value = true; };
 template <> struct is_mc<mc_f16> { static constexpr bool value = true; };
+template <> struct is_mc<pair_bf16> { static constexpr bool value = true; };   // same vector shape: whole 16-byte vectors only
 
 // ---- amp_C.multi_tensor_adam ------------------------------------------------------------------
 // lists [g, p, m, v] (+ optional p_copy).  Per-element math follows
@@ -70,7 +71,10 @@ struct DistAdamOp : OpBase {
   static constexpr int NL = COPY ? 5 : 4;
   static constexpr unsigned STORES = COPY ? 0b10111 : 0b00111;
   static constexpr bool MC = is_mc<Tg>::value || is_mc<Tc>::value;
-  static constexpr int UNROLL = MC ? B200MT_NVLS_UNROLL : B200MT_ADAM_UNROLL;
+  // peer-memory form: ONE vector per thread and 4 CTAs/SM -- 32.8 -> 23.0 ms at W = 2 against two vectors at 2 CTAs/SM (the
+  // remote loads want resident warps, not registers); the multicast form is indifferent to it (profiles/nvls_probe_r01.txt)
+  static constexpr bool PAIR = std::is_same<Tg, pair_bf16>::value;
+  static constexpr int UNROLL = PAIR ? 1 : (MC ? B200MT_NVLS_UNROLL : B200MT_ADAM_UNROLL);
   static constexpr int VEC = MC ? B200MT_NVLS_VEC : B200MT_ADAM_VEC;
   static constexpr int THREADS = 256;
   static constexpr int MIN_CTAS = (VEC * UNROLL > 8) ? 2 : 4;
@@ -280,6 +284,48 @@ extern "C" int b200mt_dist_adam_nvls(const b200mt_lists* L, int chunk_size, int3
   }
   B200MT_CHECK(!(local_grads || local_copy), "dist_adam_nvls: the measurement switches are built for BFloat16 only");
   return packed ? run(DistAdamOp<mc_f16, mc_e5m2, true>()) : run(DistAdamOp<mc_f16, mc_f16, true>());
+}
+
+// ---- b200mt_dist_adam_p2p: the sharded step of TWO ranks as one kernel over peer-mapped memory (extension).
+// lists = [p32, m32, v32, g, p_copy] with g and p_copy THIS rank's addresses inside buffers that have a twin in the peer's
+// memory at the given byte distances.  Gradients: own + peer's, summed on load; parameters: stored here and in the peer.
+extern "C" int b200mt_dist_adam_p2p(const b200mt_lists* L, int chunk_size, int32_t* noop,
+                                    const float* pt_beta1, const float* pt_beta2,
+                                    const int32_t* pt_bias_correction, const float* pt_eps,
+                                    const float* pt_weight_decay, float lr, float grad_scale, int step,
+                                    int mode, int64_t grad_peer_delta, int64_t copy_peer_delta, void* stream_) {
+  (void)noop;
+  if (check_common(L, chunk_size)) return 1;
+  B200MT_CHECK(pt_beta1 && pt_beta2 && pt_bias_correction && pt_eps && pt_weight_decay,
+               "per-tensor hyper-parameter array is NULL");
+  B200MT_CHECK(L->depth == 5, "dist_adam_p2p: expected [p32, m32, v32, g, p_copy]");
+  B200MT_CHECK(L->dtype[0] == B200MT_F32 && L->dtype[1] == B200MT_F32 && L->dtype[2] == B200MT_F32,
+               "dist_adam_p2p: p, m, v must be fp32");
+  B200MT_CHECK(L->dtype[3] == B200MT_BF16 && L->dtype[4] == B200MT_BF16, "dist_adam_p2p: g and p_copy must be BFloat16");
+  B200MT_CHECK(grad_peer_delta % 16 == 0 && copy_peer_delta % 16 == 0 && grad_peer_delta != 0 && copy_peer_delta != 0,
+               "dist_adam_p2p: the peer distances must be non-zero multiples of 16 bytes");
+  for (int t = 0; t < L->ntensors; t++) {
+    B200MT_CHECK(L->numel[t] % B200MT_NVLS_VEC == 0, "dist_adam_p2p: fragment %d has %lld elements; fragments must be "
+                 "multiples of %d elements", t, (long long)L->numel[t], B200MT_NVLS_VEC);
+    for (int d = 0; d < 5; d++) {
+      const int al = (d < 3 ? 4 : 2) * B200MT_NVLS_VEC;
+      B200MT_CHECK(((uintptr_t)L->ptrs[(size_t)d * L->ntensors + t]) % al == 0,
+                   "dist_adam_p2p: list %d fragment %d is not %d-byte aligned", d, t, al);
+    }
+  }
+  CallGuard guard(L->device);
+  if (guard.status) return 1;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  TableView tv;
+  if (acquire_table(L, 5, 5, elementwise_tiling(), stream, &tv)) return 1;
+  const long long delta[2] = {(long long)grad_peer_delta, (long long)copy_peer_delta};
+  // stream-ordered: kernels launched earlier on this stream keep the distances they were launched with
+  B200MT_CUDA(cudaMemcpyToSymbolAsync(c_pair_delta, delta, sizeof(delta), 0, cudaMemcpyHostToDevice, stream));
+  DistAdamOp<pair_bf16, pair_bf16, true> op;
+  op.pt_beta1 = pt_beta1; op.pt_beta2 = pt_beta2; op.pt_eps = pt_eps; op.pt_decay = pt_weight_decay;
+  op.pt_bias_correction = pt_bias_correction; op.lr = lr; op.grad_scale = grad_scale;
+  op.step = step; op.mode = mode;
+  return launch_stream(tv, op, stream, /*allow_pdl=*/false);   // the constant write above must be complete before the kernel starts
 }
 
 extern "C" int b200mt_contrib_adam(const b200mt_lists* L, int chunk_size, int32_t* noop, float lr,

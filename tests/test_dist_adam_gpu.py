@@ -101,11 +101,14 @@ def _worker(rank, world, port, K, zero_copy, fused, out, e5m2=False, group_size=
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("K,zero_copy,fused", [(1, False, False), (4, True, False), (1, False, True), (1, True, True)])
+@pytest.mark.parametrize("K,zero_copy,fused", [(1, False, False), (4, True, False), (1, False, True), (1, True, True),
+                                               (1, False, "multimem"), (1, True, "p2p")])
 def test_sharded_adam_matches_unsharded_world2_nccl(K, zero_copy, fused):
+    """fused: False = NCCL pipeline; True = one kernel, form picked by world size (two ranks: peer-memory loads and stores);
+    "multimem" / "p2p" force the in-switch or the peer-memory form."""
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29700 + K + (20 if fused else 0) + (40 if zero_copy else 0)
+    port = 29700 + K + (20 if fused else 0) + (40 if zero_copy else 0) + (5 if isinstance(fused, str) else 0)
     procs = [ctx.Process(target=_worker, args=(r, 2, port, K, zero_copy, fused, q)) for r in range(2)]
     for p in procs:
         p.start()

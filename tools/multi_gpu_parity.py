@@ -130,7 +130,11 @@ def sharded_adam_parity(opt, sample_elems=16 << 20):
     scale = opt._combined_scale()
 
     # ---- the reduced gradient the step kernel consumed
-    if fused:
+    if fused and getattr(opt, "_fused_form", None) == "p2p":
+        # two ranks over peer memory: the kernel's load IS fp32(own) + fp32(peer) rounded once to the gradient type --
+        # bit for bit the fp32 all-reduce above, rounded
+        gred = [s_.to(low) for s_ in gsum]
+    elif fused:
         # never materialised by the fused kernel: repeat exactly its load (multimem.ld_reduce through the same
         # multicast addresses) with the stand-alone reduce-scatter kernel; the gradients are untouched by the step
         esz = opt._flat_grads.element_size()
