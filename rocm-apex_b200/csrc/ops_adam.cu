@@ -77,7 +77,11 @@ struct DistAdamOp : OpBase {
   static constexpr int UNROLL = PAIR ? 1 : (MC ? B200MT_NVLS_UNROLL : B200MT_ADAM_UNROLL);
   static constexpr int VEC = MC ? B200MT_NVLS_VEC : B200MT_ADAM_VEC;
   static constexpr int THREADS = 256;
+#ifdef B200MT_NVLS_MIN_CTAS
+  static constexpr int MIN_CTAS = MC ? B200MT_NVLS_MIN_CTAS : ((VEC * UNROLL > 8) ? 2 : 4);
+#else
   static constexpr int MIN_CTAS = (VEC * UNROLL > 8) ? 2 : 4;
+#endif
   struct State { float b1, b2, eps, decay, bc1, bc2, rbc1, rbc2, rgs; };
   const float *pt_beta1, *pt_beta2, *pt_eps, *pt_decay;
   const int* pt_bias_correction;
