@@ -132,3 +132,37 @@ def test_no_gradients_at_all_gives_no_buckets(GroupCache):
     params[1].grad = torch.ones_like(params[1])
     b = c.buckets(opt, 0, group, init_state)
     assert len(b) == 1 and len(b[0][1]) == 1 and b[0][1][0] is params[1]
+
+
+def test_native_row_check_codes():
+    """csrc/packer.cpp: check_rows -- the one native loop that decides whether a prepared [g, p, s0, s1] handle may be
+    reused: 0 = gradients at the cached addresses and state tensors unchanged, 1 = a gradient moved / vanished / changed
+    type, 2 = a state tensor was replaced.  Works on any device's tensors: exercised here on CPU."""
+    import numpy as np
+    import pytest
+    import torch
+    import _b200mt as mt
+    if mt.check_rows is None:
+        pytest.skip("native packer not built")
+    ps = [torch.nn.Parameter(torch.randn(n)) for n in (5, 64, 1000)]
+    for p in ps:
+        p.grad = torch.randn_like(p)
+    states = [{"exp_avg": torch.zeros_like(p), "exp_avg_sq": torch.zeros_like(p), "other": 1} for p in ps]
+    rows = [(p, st, st["exp_avg"], st["exp_avg_sq"]) for p, st in zip(ps, states)]
+    ptrs = np.array([p.grad.data_ptr() for p in ps], dtype=np.uint64)
+    f32 = mt.F32
+    assert mt.check_rows(rows, "exp_avg", "exp_avg_sq", ptrs.ctypes.data, f32) == 0
+    ps[1].grad.add_(1.0)                                         # values change, addresses do not
+    assert mt.check_rows(rows, "exp_avg", "exp_avg_sq", ptrs.ctypes.data, f32) == 0
+    old = ps[1].grad
+    ps[1].grad = torch.randn_like(ps[1])                         # a gradient somewhere else
+    assert mt.check_rows(rows, "exp_avg", "exp_avg_sq", ptrs.ctypes.data, f32) == 1
+    ps[1].grad = None                                            # ... or gone
+    assert mt.check_rows(rows, "exp_avg", "exp_avg_sq", ptrs.ctypes.data, f32) == 1
+    ps[1].grad = old
+    assert mt.check_rows(rows, "exp_avg", "exp_avg_sq", ptrs.ctypes.data, f32) == 0
+    assert mt.check_rows(rows, "exp_avg", "exp_avg_sq", ptrs.ctypes.data, mt.F16) == 1     # cached dtype no longer matches
+    states[2]["exp_avg_sq"] = torch.zeros_like(ps[2])            # a state tensor replaced by the user
+    assert mt.check_rows(rows, "exp_avg", "exp_avg_sq", ptrs.ctypes.data, f32) == 2
+    with pytest.raises(RuntimeError, match="malformed"):
+        mt.check_rows([(ps[0], states[0], None)], "exp_avg", "exp_avg_sq", ptrs.ctypes.data, f32)
