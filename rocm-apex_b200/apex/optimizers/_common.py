@@ -27,17 +27,19 @@ class GroupCache(object):
     tensor (`state[p][name] is cached`), and which parameters have a gradient at all.  Any mismatch falls back to the
     slow pass, which is the reference's loop with its checks and error messages."""
 
-    def __init__(self, optimizer_name, state_names):
+    def __init__(self, optimizer_name, state_names, grad_handles=False):
         self.name = optimizer_name
         self.names = tuple(state_names)
         assert len(self.names) == 2, "specialised for two state tensors per parameter"
         self.groups = {}
+        self.grad_handles = grad_handles      # also keep a depth-1 handle over the gradients alone (FusedLAMB's norm)
 
     def clear(self):
         for c in self.groups.values():
             for b in c[4]:
-                if b[4].get("prep") is not None:
-                    b[4]["prep"].release()
+                for k in ("prep", "prep_g"):
+                    if b[4].get(k) is not None:
+                        b[4][k].release()
         self.groups = {}
 
     def buckets(self, opt, gi, group, init_state):
@@ -90,8 +92,7 @@ class GroupCache(object):
         self._slow(opt, gi, group, init_state)
         return [self._maybe_prepare(b, [r[0].grad for r in b[0]]) for b in self.groups[gi][4]]
 
-    @staticmethod
-    def _maybe_prepare(bucket, gs):
+    def _maybe_prepare(self, bucket, gs):
         import _b200mt as mt
         rows, ps, s0, s1, h = bucket
         lists = [gs, ps, s0, s1]
@@ -99,14 +100,32 @@ class GroupCache(object):
             h["prep"].release()
             h["prep"] = None
             h["misses"] = h.get("misses", 0) + 1
+        if h.get("prep_g") is not None:
+            h["prep_g"].release()
+            h["prep_g"] = None
         if h.get("misses", 0) >= 3 or any(g.is_sparse for g in gs):
             return lists
         try:
             h["prep"] = mt.prepare(lists, keep=False)      # the gradients are not held: their addresses are re-checked
             h["code"] = mt.dtype_code(gs[0])
+            if self.grad_handles:
+                h["prep_g"] = mt.prepare([gs], keep=False)  # same addresses, so the same check covers it
             return h["prep"]
         except RuntimeError:
             return lists                                   # let the plain call report whatever is wrong with the lists
+
+    def launch_sets_with_grads(self, opt, gi, group, init_state):
+        """launch_sets() plus, per entry, what a norm over the bucket's gradients alone should be handed: the depth-1
+        handle that was prepared together with the four-list one, else the list of gradients.  -> [(set, grads)]"""
+        sets = self.launch_sets(opt, gi, group, init_state)
+        out = []
+        for s, bucket in zip(sets, self.groups[gi][4]):
+            if isinstance(s, list):
+                out.append((s, s[0]))
+            else:
+                g = bucket[4].get("prep_g")
+                out.append((s, g if g is not None else [r[0].grad for r in bucket[0]]))
+        return out
 
     def _fast(self, c):
         n0, n1 = self.names

@@ -22,7 +22,8 @@ class FusedLAMB(torch.optim.Optimizer):
         self.adam_w_mode = 1 if adam_w_mode else 0
         self.set_grad_none = set_grad_none
         self.use_nvlamb = use_nvlamb
-        self._lists = _common.GroupCache("FusedLAMB", ("exp_avg", "exp_avg_sq"))
+        self._lists = _common.GroupCache("FusedLAMB", ("exp_avg", "exp_avg_sq"), grad_handles=True)
+        self._zero_norm = torch.zeros(1, device=self.param_groups[0]["params"][0].device)   # pads the list of norms to two
 
     def zero_grad(self, set_to_none=None):
         if self.set_grad_none if set_to_none is None else set_to_none:
@@ -39,31 +40,41 @@ class FusedLAMB(torch.optim.Optimizer):
 
     def _global_grad_norm(self, per_group):
         """sqrt(||g32||^2 + ||g16||^2 ...): one l2norm per dtype, then the l2norm of those norms
-        (apex/optimizers/fused_lamb.py:107-136)."""
-        device = self.param_groups[0]["params"][0].device
-        grads = {}
-        for buckets in per_group:
-            for gs, ps, _, _ in buckets:
-                if gs:
-                    grads.setdefault(ps[0].dtype, []).extend(gs)
-        norms = [multi_tensor_applier(self.multi_tensor_l2norm, self._dummy_overflow_buf, [g], False)[0]
-                 for g in grads.values()]
+        (apex/optimizers/fused_lamb.py:107-136).  A dtype that lives in one bucket -- one parameter group, the usual
+        case -- is normed through the bucket's prepared gradient handle; a dtype spread over several groups is
+        normed as one concatenated list, as the reference does."""
+        by_dtype = {}
+        for gi, sets in enumerate(per_group):
+            for (_, grads), bucket in zip(sets, self._lists.groups[gi][4]):
+                by_dtype.setdefault(bucket[1][0].dtype, []).append((grads, bucket))
+        norms = []
+        for entries in by_dtype.values():
+            if len(entries) == 1:
+                grads = entries[0][0]
+            else:
+                grads = []
+                for g, bucket in entries:
+                    grads.extend(g if isinstance(g, list) else [r[0].grad for r in bucket[0]])
+            norms.append(multi_tensor_applier(self.multi_tensor_l2norm, self._dummy_overflow_buf,
+                                              grads if not isinstance(grads, list) else [grads], False)[0])
         while len(norms) < 2:
-            norms.append(torch.zeros(1, device=device))
+            norms.append(self._zero_norm)
         return multi_tensor_applier(self.multi_tensor_l2norm, self._dummy_overflow_buf, [norms], False)[0]
 
     @torch.no_grad()
     def step(self, closure=None):
         loss = closure() if closure is not None else None
-        # [g, p, exp_avg, exp_avg_sq] per group and dtype: the reference's per-parameter loops (:107-136,149-190), memoised
-        per_group = [self._lists.buckets(self, gi, group, self._init_state) for gi, group in enumerate(self.param_groups)]
+        # [g, p, exp_avg, exp_avg_sq] per group and dtype: the reference's per-parameter loops (:107-136,149-190), memoised,
+        # and handed over as prepared handles while the gradients keep their addresses (_common.GroupCache.launch_sets)
+        per_group = [self._lists.launch_sets_with_grads(self, gi, group, self._init_state)
+                     for gi, group in enumerate(self.param_groups)]
         global_grad_norm = self._global_grad_norm(per_group)
         max_grad_norm = self.defaults["max_grad_norm"]
-        for group, buckets in zip(self.param_groups, per_group):
+        for group, sets in zip(self.param_groups, per_group):
             group["step"] = group.get("step", 0) + 1
             beta1, beta2 = group["betas"]
-            for lists in buckets:
-                multi_tensor_applier(self.multi_tensor_lamb, self._dummy_overflow_buf, list(lists), group["lr"],
+            for lists, _ in sets:
+                multi_tensor_applier(self.multi_tensor_lamb, self._dummy_overflow_buf, lists, group["lr"],
                                      beta1, beta2, group["eps"], group["step"],
                                      1 if group["bias_correction"] else 0, group["weight_decay"],
                                      1 if group["grad_averaging"] else 0, self.adam_w_mode,

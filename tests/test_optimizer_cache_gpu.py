@@ -229,3 +229,58 @@ def test_fused_sgd_prepared_handle_follows_the_gradients():
     fx.state[x[3]]["momentum_buffer"] = fx.state[x[3]]["momentum_buffer"].clone()      # state replaced: memo rebuilt
     fx.step(); ty.step()
     assert same(x, y, tol=1e-5)
+
+
+@pytest.mark.parametrize("two_groups", [False, True])
+def test_fused_lamb_prepared_handles_match_plain_lists(two_groups):
+    """FusedLAMB norms the gradients through a depth-1 handle prepared together with the [g, p, m, v] one (a dtype that
+    sits in one bucket) or as one concatenated list (a dtype spread over two groups); a twin that is only ever given
+    plain lists must end up bit-identical, through gradients rewritten in place, moved, and missing."""
+    import _b200mt as mt
+    from apex.optimizers import FusedLAMB
+    if mt.check_rows is None:
+        pytest.skip("native packer not built")
+    x, y = make(seed=7)
+    h16 = torch.nn.Parameter((torch.randn(300, device="cuda") * 0.1).half())
+    x, y = x + [h16], y + [torch.nn.Parameter(h16.detach().clone())]
+    kw = dict(lr=1e-2, weight_decay=0.01, max_grad_norm=0.5)
+    groups = lambda ps: [{"params": ps[:4] + ps[6:]}, {"params": ps[4:6], "weight_decay": 0.0}] if two_groups else ps
+    fx, fy = FusedLAMB(groups(x), **kw), FusedLAMB(groups(y), **kw)
+    fy._lists._maybe_prepare = lambda bucket, gs: [gs, bucket[1], bucket[2], bucket[3]]     # the twin never prepares
+    g = torch.Generator(device="cuda").manual_seed(8)
+
+    def fresh_grads(keep=None):
+        for p, q in zip(x, y):
+            p.grad = torch.randn(p.shape, generator=g, device="cuda").to(p.dtype); q.grad = p.grad.clone()
+            if keep is not None:
+                keep.append(p.grad)
+
+    fresh_grads()
+    fx.step(); fy.step()
+    assert same(x, y, tol=0.0)
+    b0 = fx._lists.groups[0][4]
+    assert [b[1][0].dtype for b in b0] == [torch.float32, torch.float16]
+    assert all(b[4].get("prep") is not None and b[4].get("prep_g") is not None and b[4]["prep_g"].depth == 1 for b in b0)
+    assert all(b[4].get("prep") is None for b in fy._lists.groups[0][4])
+    first = [b[4]["prep_g"] for b in b0]
+    up0 = mt.lib.b200mt_table_uploads()
+    for it in range(3):                                   # in place (the update kernel has overwritten g): same handles
+        for p, q in zip(x, y):
+            p.grad.copy_(torch.randn(p.shape, generator=g, device="cuda")); q.grad.copy_(p.grad)
+        fx.step(); fy.step()
+        assert same(x, y, tol=0.0)
+        assert [b[4]["prep_g"] for b in fx._lists.groups[0][4]] == first
+    if not two_groups:                                    # nothing but the list of two norms can have been uploaded
+        assert mt.lib.b200mt_table_uploads() - up0 <= 3
+    keep = []
+    for it in range(5):                                   # gradients somewhere else every step: back to plain lists
+        fresh_grads(keep)
+        fx.step(); fy.step()
+        assert same(x, y, tol=0.0)
+    assert all(b[4].get("prep") is None and b[4].get("prep_g") is None for b in fx._lists.groups[0][4])
+    x[1].grad, y[1].grad = None, None                     # a parameter without gradient, then with one again
+    fx.step(); fy.step()
+    fresh_grads()
+    fx.step(); fy.step()
+    assert same(x, y, tol=0.0)
+    fx._lists.clear()
