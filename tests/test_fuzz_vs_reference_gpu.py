@@ -242,3 +242,135 @@ def test_fuzz_lamb(amp_C, ref, seed):
     for i, (a, b) in enumerate(zip(lists[2], rl[2])):
         assert_close_rel(a, b, rtol=1e-6, scale=opnd[i], what="m[%d] args %r" % (i, args))
     assert_rel_pure(lists[3], rl[3], 2e-6, "v")
+
+
+@pytest.mark.parametrize("seed", SEEDS)
+def test_fuzz_l2norm_scale(amp_C, ref, seed):
+    c = Case(seed, max_tensors=100)
+    r = c.rng
+    in_t, out_t = r.choice([(torch.float32, torch.float32), (torch.float16, torch.float32), (torch.float32, torch.float16),
+                            (torch.float16, torch.float16)])   # the reference dispatches fp32 / fp16 only here
+    xs, outs = c.views(in_t, scale=r.choice([1.0, 20.0])), c.views(out_t)
+    r_outs = [o.clone() for o in outs]
+    per_tensor = r.random() < 0.6
+    s = r.choice([0.125, 1.0 / 1024.0, 2.0])
+    f, rf = flag(), flag()
+    n, p = amp_C.multi_tensor_l2norm_scale(c.chunk, f, [xs, outs], s, per_tensor)
+    rn, rp = ref.multi_tensor_l2norm_scale(c.chunk, rf, [xs, r_outs], s, per_tensor)
+    assert int(f) == int(rf) == 0
+    assert_rel_pure(n, rn, 1e-5, "norm")
+    if per_tensor:
+        assert_rel_pure(p, rp, 1e-5, "per-tensor norms")
+    for k, (a, b) in enumerate(zip(outs, r_outs)):
+        assert same_bits(a, b), "tensor %d" % k
+
+
+@pytest.mark.parametrize("seed", SEEDS)
+def test_fuzz_lamb_mp(amp_C, ref, seed):
+    c = Case(seed, max_tensors=100)
+    r = c.rng
+    depth = r.choice([4, 5])
+    gdt = torch.float16 if depth == 5 else torch.float32
+    scale = r.choice([1.0, 128.0, 1024.0])
+    g = c.views(gdt, scale=scale if gdt == torch.float32 else min(scale, 128.0))
+    _, p, m, v = adam_state(c, torch.float32)
+    lists = [g, p, m, v]
+    if depth == 5:
+        lists.append([x.to(torch.float16) for x in p])
+    rl = clone(lists)
+    lr = torch.tensor([r.choice([2e-3, 1e-2])], device="cuda")
+    step = torch.tensor([r.randrange(1, 300)], device="cuda", dtype=torch.int32)
+    inv_scale = torch.tensor([1.0 / scale], device="cuda")
+    found_inf = torch.zeros(1, device="cuda")
+    max_norm = torch.tensor([r.choice([0.5, 1.0, 1e6]) * scale], device="cuda")
+    f, rf = flag(), flag()
+    gn, _ = amp_C.multi_tensor_l2norm_mp(c.chunk, f, [g], False)
+    rgn, _ = ref.multi_tensor_l2norm_mp(c.chunk, rf, [rl[0]], False)
+    assert_rel_pure(gn, rgn, 1e-5, "gradient norm")
+    args = (r.choice([0.8, 0.9]), r.choice([0.95, 0.999]), 1e-6)
+    tail = (step, r.choice([0, 1]), r.choice([0.0, 0.01]), r.choice([0, 1]), r.choice([0, 1]))
+    nvlamb = r.random() < 0.5
+    opnd = operand_scale([[x.float() / scale for x in g], p, m])
+    amp_C.multi_tensor_lamb_mp(c.chunk, f, lists, lr, *args, *tail, gn, max_norm, nvlamb, found_inf, inv_scale)
+    ref.multi_tensor_lamb_mp(c.chunk, rf, rl, lr, *args, *tail, gn.clone(), max_norm, nvlamb, found_inf, inv_scale)
+    assert int(f) == int(rf) == 0
+    what = "depth %d args %r %r nvlamb %r" % (depth, args, tail[1:], nvlamb)
+    for k, rt in ((0, 1e-3 if depth == 5 else 2e-6), (1, 1e-5)):
+        for i, (a, b) in enumerate(zip(lists[k], rl[k])):
+            assert_close_rel(a, b, rtol=rt, scale="self", what="list %d[%d] %s" % (k, i, what))
+    for i, (a, b) in enumerate(zip(lists[2], rl[2])):
+        assert_close_rel(a, b, rtol=1e-6, scale=opnd[i], what="m[%d] %s" % (i, what))
+    assert_rel_pure(lists[3], rl[3], 2e-6, "v")
+    if depth == 5:
+        for a, b in zip(lists[4], rl[4]):
+            assert_close_rel(a, b, rtol=1e-3, scale="self", what="fp16 model copy")
+
+
+@pytest.mark.parametrize("seed", SEEDS)
+def test_fuzz_sharded_adam_kernel(seed):
+    """distributed_adam_cuda.multi_tensor_fused_adam ([p, m, v, g(, p_copy)], per-tensor hyper-parameter arrays)."""
+    import distributed_adam_cuda as ours
+    refm = load_ref("distributed_adam_cuda_ref")
+    if refm is None:
+        pytest.skip("oracle/_ref/distributed_adam_cuda_ref.so not built")
+    c = Case(seed, max_tensors=100)
+    r = c.rng
+    gdt = r.choice(DTS)
+    depth = r.choice([4, 5])
+    gscale = r.choice([1.0, 32.0])
+    _, p, m, v = adam_state(c, torch.float32)
+    g = c.views(gdt, scale=gscale)
+    lists = [p, m, v, g]
+    if depth == 5:
+        lists.append([torch.zeros(n, device="cuda", dtype=gdt) for n in c.sizes])
+    rl = clone(lists)
+    T = c.T
+    rnd = lambda lo, hi: torch.tensor([r.uniform(lo, hi) for _ in range(T)], device="cuda")
+    b1, b2, eps, wd = rnd(0.8, 0.95), rnd(0.95, 0.999), rnd(1e-8, 1e-6), rnd(0.0, 0.1)
+    bc = torch.tensor([r.choice([0, 1]) for _ in range(T)], device="cuda", dtype=torch.int32)
+    args = (r.choice([1e-4, 1e-3]), gscale, r.randrange(1, 1000), r.choice([0, 1]))
+    opnd = operand_scale([[x.float() / gscale for x in g], p, m])
+    ours.multi_tensor_fused_adam(c.chunk, flag(), lists, b1, b2, bc, eps, wd, *args)
+    refm.multi_tensor_fused_adam(c.chunk, flag(), rl, b1, b2, bc, eps, wd, *args)
+    for i, (a, b) in enumerate(zip(lists[0], rl[0])):
+        assert_close_rel(a, b, rtol=1e-6, scale="self", what="p[%d] args %r" % (i, args))
+    for i, (a, b) in enumerate(zip(lists[1], rl[1])):
+        assert_close_rel(a, b, rtol=1e-6, scale=opnd[i], what="m[%d] args %r" % (i, args))
+    assert_rel_pure(lists[2], rl[2], 1e-6, "v")
+    if depth == 5:
+        for a, b in zip(lists[4], lists[0]):
+            assert torch.equal(a, b.to(gdt))             # the copy is exactly the rounded master weight
+        for a, b in zip(lists[4], rl[4]):
+            assert_close_rel(a, b, rtol=ULP[gdt] if gdt != torch.float32 else 1e-6, scale="self", what="p_copy")
+
+
+@pytest.mark.parametrize("seed", SEEDS[:12])
+def test_fuzz_contrib_adam_mt(seed):
+    """fused_adam_cuda.adam_mt ([p, m, v, g(, p_copy)], the legacy contrib FusedAdam kernel)."""
+    import fused_adam_cuda as ours
+    refm = load_ref("fused_adam_cuda_ref")
+    if refm is None:
+        pytest.skip("oracle/_ref/fused_adam_cuda_ref.so not built")
+    c = Case(seed, max_tensors=100)
+    r = c.rng
+    depth = r.choice([4, 5])
+    gscale = r.choice([1.0, 32.0])
+    _, p, m, v = adam_state(c, torch.float32)
+    g = c.views(torch.float16, scale=gscale)
+    lists = [p, m, v, g]
+    if depth == 5:
+        lists.append([torch.zeros(n, device="cuda", dtype=torch.float16) for n in c.sizes])
+    rl = clone(lists)
+    args = (r.choice([1e-4, 1e-3]), r.choice([0.8, 0.9]), r.choice([0.95, 0.999]), r.choice([1e-8, 1e-6]), gscale,
+            r.randrange(1, 1000), r.choice([0, 1]), r.choice([0, 1]), r.choice([0.0, 0.01]))
+    opnd = operand_scale([[x.float() / gscale for x in g], p, m])
+    ours.adam_mt(c.chunk, flag(), lists, *args)
+    refm.adam_mt(c.chunk, flag(), rl, *args)
+    for i, (a, b) in enumerate(zip(lists[0], rl[0])):
+        assert_close_rel(a, b, rtol=1e-6, scale="self", what="p[%d] args %r" % (i, args))
+    for i, (a, b) in enumerate(zip(lists[1], rl[1])):
+        assert_close_rel(a, b, rtol=1e-6, scale=opnd[i], what="m[%d] args %r" % (i, args))
+    assert_rel_pure(lists[2], rl[2], 1e-6, "v")
+    if depth == 5:
+        for a, b in zip(lists[4], rl[4]):
+            assert_close_rel(a, b, rtol=1e-3, scale="self", what="p_copy")
