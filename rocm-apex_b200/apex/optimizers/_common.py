@@ -1,4 +1,6 @@
 """Helpers shared by the fused optimizers of this mirror."""
+import collections
+
 import torch
 
 from ..multi_tensor_apply import multi_tensor_applier
@@ -15,6 +17,14 @@ def require_extension(name):
 
 def overflow_buf(device=None):
     return torch.zeros(1, dtype=torch.int32, device=device if device is not None else "cuda")
+
+
+# What GroupCache remembers of one param group, and of one parameter dtype inside it.  `rows` is a list of
+# (param, state_dict, state0_tensor, state1_tensor) tuples -- the layout csrc/packer.cpp: check_rows walks -- and `handles` a dict
+# with the prepared list handles ("prep": [g, p, s0, s1]; "prep_g": [g] alone), the gradient dtype code they were made for and
+# the number of consecutive steps the gradients had moved.
+Group = collections.namedtuple("Group", "state params nparams idle buckets")
+Bucket = collections.namedtuple("Bucket", "rows params state0 state1 handles")
 
 
 class GroupCache(object):
@@ -36,16 +46,16 @@ class GroupCache(object):
 
     def clear(self):
         for c in self.groups.values():
-            for b in c[4]:
+            for b in c.buckets:
                 for k in ("prep", "prep_g"):
-                    if b[4].get(k) is not None:
-                        b[4][k].release()
+                    if b.handles.get(k) is not None:
+                        b.handles[k].release()
         self.groups = {}
 
     def buckets(self, opt, gi, group, init_state):
         """-> list of (grads, params, state0, state1) lists, one entry per parameter dtype (fp32 first)."""
         c = self.groups.get(gi)
-        if c is not None and c[0] is opt.state and c[1] is group["params"] and c[2] == len(group["params"]):
+        if c is not None and c.state is opt.state and c.params is group["params"] and c.nparams == len(group["params"]):
             out = self._fast(c)
             if out is not None:
                 return out
@@ -62,13 +72,13 @@ class GroupCache(object):
             return [list(b) for b in self.buckets(opt, gi, group, init_state)]
         n0, n1 = self.names
         c = self.groups.get(gi)
-        if c is not None and c[0] is opt.state and c[1] is group["params"] and c[2] == len(group["params"]) \
-                and all(p.grad is None for p in c[3]):
+        if c is not None and c.state is opt.state and c.params is group["params"] and c.nparams == len(group["params"]) \
+                and all(p.grad is None for p in c.idle):
             out = []
-            for bucket in c[4]:
-                h = bucket[4]
+            for bucket in c.buckets:
+                h = bucket.handles
                 if h.get("prep") is not None:
-                    rc = mt.check_rows(bucket[0], n0, n1, h["prep"].ptrs.ctypes.data, h["code"])
+                    rc = mt.check_rows(bucket.rows, n0, n1, h["prep"].ptrs.ctypes.data, h["code"])
                     if rc == 0:
                         h["misses"] = 0
                         out.append(h["prep"])
@@ -77,7 +87,7 @@ class GroupCache(object):
                         out = None
                         break
                 gs = []
-                for p, st, t0, t1 in bucket[0]:
+                for p, st, t0, t1 in bucket.rows:
                     g = p.grad
                     if g is None or st[n0] is not t0 or st[n1] is not t1:
                         gs = None
@@ -90,7 +100,7 @@ class GroupCache(object):
             if out is not None:
                 return out
         self._slow(opt, gi, group, init_state)
-        return [self._maybe_prepare(b, [r[0].grad for r in b[0]]) for b in self.groups[gi][4]]
+        return [self._maybe_prepare(b, [r[0].grad for r in b.rows]) for b in self.groups[gi].buckets]
 
     def _maybe_prepare(self, bucket, gs):
         import _b200mt as mt
@@ -119,21 +129,21 @@ class GroupCache(object):
         handle that was prepared together with the four-list one, else the list of gradients.  -> [(set, grads)]"""
         sets = self.launch_sets(opt, gi, group, init_state)
         out = []
-        for s, bucket in zip(sets, self.groups[gi][4]):
+        for s, bucket in zip(sets, self.groups[gi].buckets):
             if isinstance(s, list):
                 out.append((s, s[0]))
             else:
-                g = bucket[4].get("prep_g")
-                out.append((s, g if g is not None else [r[0].grad for r in bucket[0]]))
+                g = bucket.handles.get("prep_g")
+                out.append((s, g if g is not None else [r[0].grad for r in bucket.rows]))
         return out
 
     def _fast(self, c):
         n0, n1 = self.names
-        for p in c[3]:                       # parameters that had no gradient when the cache was built
+        for p in c.idle:                     # parameters that had no gradient when the cache was built
             if p.grad is not None:
                 return None
         out = []
-        for rows, ps, s0, s1, _ in c[4]:
+        for rows, ps, s0, s1, _ in c.buckets:
             gs = []
             add = gs.append
             for p, st, t0, t1 in rows:
@@ -165,9 +175,9 @@ class GroupCache(object):
             if not rows:
                 continue
             ps, s0, s1 = [r[0] for r in rows], [r[2] for r in rows], [r[3] for r in rows]
-            cached.append((rows, ps, s0, s1, {}))
+            cached.append(Bucket(rows, ps, s0, s1, {}))
             out.append(([r[0].grad for r in rows], ps, s0, s1))
-        self.groups[gi] = (opt.state, group["params"], len(group["params"]), idle, cached)
+        self.groups[gi] = Group(opt.state, group["params"], len(group["params"]), idle, cached)
         return out
 
 

@@ -45,8 +45,8 @@ class FusedLAMB(torch.optim.Optimizer):
         normed as one concatenated list, as the reference does."""
         by_dtype = {}
         for gi, sets in enumerate(per_group):
-            for (_, grads), bucket in zip(sets, self._lists.groups[gi][4]):
-                by_dtype.setdefault(bucket[1][0].dtype, []).append((grads, bucket))
+            for (_, grads), bucket in zip(sets, self._lists.groups[gi].buckets):
+                by_dtype.setdefault(bucket.params[0].dtype, []).append((grads, bucket))
         norms = []
         for entries in by_dtype.values():
             if len(entries) == 1:
@@ -54,7 +54,7 @@ class FusedLAMB(torch.optim.Optimizer):
             else:
                 grads = []
                 for g, bucket in entries:
-                    grads.extend(g if isinstance(g, list) else [r[0].grad for r in bucket[0]])
+                    grads.extend(g if isinstance(g, list) else [r[0].grad for r in bucket.rows])
             norms.append(multi_tensor_applier(self.multi_tensor_l2norm, self._dummy_overflow_buf,
                                               grads if not isinstance(grads, list) else [grads], False)[0])
         while len(norms) < 2:

@@ -1,11 +1,16 @@
 """FusedSGD (reference: apex/optimizers/fused_sgd.py:6-227).  With amp master weights it consumes the
 still-scaled gradients directly -- the unscale rides in the kernel as `1/most_recent_scale` -- and
 writes the fp16 model weights in the same pass."""
+import collections
+
 import torch
 from torch.optim.optimizer import required
 
 from ..multi_tensor_apply import multi_tensor_applier
 from . import _common
+
+# one parameter dtype of a memoised group: rows of (param, state_dict, momentum, momentum) as csrc/packer.cpp: check_rows walks them
+_Bucket = collections.namedtuple("_Bucket", "rows params momentums handles")
 
 
 class FusedSGD(torch.optim.Optimizer):
@@ -79,7 +84,7 @@ class FusedSGD(torch.optim.Optimizer):
         # the lists are memoised and a step only re-reads p.grad and checks by identity that nothing moved
         # (see _common.GroupCache for the rules).
         c = self._sets.get(gid)
-        if c is not None and c[0] is self.state and c[1] is group["params"] and c[2] == len(group["params"]):
+        if c is not None and c.state is self.state and c.params is group["params"] and c.nparams == len(group["params"]):
             sets = self._memoised_sets(c)
             if sets is not None:
                 return sets
@@ -89,10 +94,10 @@ class FusedSGD(torch.optim.Optimizer):
             moms, first = self.get_momentums(ps)
             all_warm = all_warm and not (first and ps)
             sets.append(([[p.grad for p in ps], ps, moms], first))
-            rows_by_dt.append(([(p, self.state[p], m, m) for p, m in zip(ps, moms)], ps, moms, {}))
+            rows_by_dt.append(_Bucket([(p, self.state[p], m, m) for p, m in zip(ps, moms)], ps, moms, {}))
         if all_warm:
             idle = [p for p in group["params"] if p.grad is None]
-            self._sets[gid] = (self.state, group["params"], len(group["params"]), idle, rows_by_dt)
+            self._sets[gid] = _common.Group(self.state, group["params"], len(group["params"]), idle, rows_by_dt)
         else:
             self._sets.pop(gid, None)
         return sets
@@ -103,11 +108,11 @@ class FusedSGD(torch.optim.Optimizer):
         where they sat last step (one native loop checks addresses and the identity of the momentum buffers; see
         _common.GroupCache.launch_sets), else as plain lists."""
         import _b200mt as mt
-        for p in c[3]:
+        for p in c.idle:
             if p.grad is not None:
                 return None
         sets = []
-        for rows, ps, moms, h in c[4]:
+        for rows, ps, moms, h in c.buckets:
             if not rows:
                 sets.append(([[], ps, moms], False))
                 continue

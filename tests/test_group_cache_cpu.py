@@ -57,9 +57,9 @@ def test_steady_state_reuses_lists_and_rereads_grads(GroupCache):
     assert all(a is opt.state[p]["exp_avg"] for a, p in zip(b1[0][2], params))
     for p in params:                       # backward after zero_grad(set_to_none=True): new gradient tensors
         p.grad = torch.full_like(p, 2.0)
-    rows = c.groups[0][4]
+    rows = c.groups[0].buckets
     b2 = c.buckets(opt, 0, group, init_state)
-    assert c.groups[0][4] is rows                                   # memo kept
+    assert c.groups[0].buckets is rows                                   # memo kept
     assert all(a is p.grad for a, p in zip(b2[0][0], params))       # gradients are the new ones
     assert b2[0][1] is b1[0][1] and b2[0][2] is b1[0][2]            # the other columns are the memoised lists
 
@@ -68,39 +68,39 @@ def test_every_change_the_reference_loop_would_see_forces_the_slow_pass(GroupCac
     c = GroupCache("FusedAdam", ("exp_avg", "exp_avg_sq"))
     opt, group, params = make()
     c.buckets(opt, 0, group, init_state)
-    rows = c.groups[0][4]
+    rows = c.groups[0].buckets
 
     params[2].grad = None                                           # a gradient disappears
     b = c.buckets(opt, 0, group, init_state)
-    assert c.groups[0][4] is not rows and len(b[0][0]) == 4 and all(q is not params[2] for q in b[0][1])
-    rows = c.groups[0][4]
+    assert c.groups[0].buckets is not rows and len(b[0][0]) == 4 and all(q is not params[2] for q in b[0][1])
+    rows = c.groups[0].buckets
     params[2].grad = torch.ones_like(params[2])                     # ... and comes back
     b = c.buckets(opt, 0, group, init_state)
-    assert c.groups[0][4] is not rows and len(b[0][0]) == 5
-    rows = c.groups[0][4]
+    assert c.groups[0].buckets is not rows and len(b[0][0]) == 5
+    rows = c.groups[0].buckets
 
     new_m = torch.zeros_like(params[0])                             # a state tensor is replaced in place
     opt.state[params[0]]["exp_avg"] = new_m
     b = c.buckets(opt, 0, group, init_state)
-    assert c.groups[0][4] is not rows and b[0][2][0] is new_m
-    rows = c.groups[0][4]
+    assert c.groups[0].buckets is not rows and b[0][2][0] is new_m
+    rows = c.groups[0].buckets
 
     old_state = opt.state                                           # load_state_dict: a new state mapping
     opt.state = defaultdict(dict, {p: dict(st) for p, st in old_state.items()})
     c.buckets(opt, 0, group, init_state)
-    assert c.groups[0][4] is not rows and c.groups[0][0] is opt.state
-    rows = c.groups[0][4]
+    assert c.groups[0].buckets is not rows and c.groups[0].state is opt.state
+    rows = c.groups[0].buckets
 
     group["params"] = list(group["params"])                         # amp swaps the list object of a group
     c.buckets(opt, 0, group, init_state)
-    assert c.groups[0][4] is not rows
-    rows = c.groups[0][4]
+    assert c.groups[0].buckets is not rows
+    rows = c.groups[0].buckets
 
     extra = torch.nn.Parameter(torch.zeros(7))                      # a parameter appended to the same list
     extra.grad = torch.ones(7)
     group["params"].append(extra)
     b = c.buckets(opt, 0, group, init_state)
-    assert c.groups[0][4] is not rows and len(b[0][0]) == 6 and "exp_avg" in opt.state[extra]
+    assert c.groups[0].buckets is not rows and len(b[0][0]) == 6 and "exp_avg" in opt.state[extra]
 
 
 def test_buckets_by_dtype_and_reference_error_messages(GroupCache):

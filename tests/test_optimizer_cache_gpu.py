@@ -50,7 +50,7 @@ def test_fused_adam_cache_tracks_grads_state_and_groups():
             return super().step(*args, **kwargs)
 
     fa, ta = FusedAdam(a[:4], **kw), Uncached(b[:4], **kw)
-    hits = lambda: fa._lists.groups[0][4]
+    hits = lambda: fa._lists.groups[0].buckets
     for it in range(3):                                   # cache built on step 0, reused after
         set_grads(a, b, it)
         fa.step(); ta.step()
@@ -149,7 +149,7 @@ def test_fused_adam_prepared_handle_follows_the_gradients():
     kw = dict(lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=0.01)
     x, y = make(seed=3)
     fx, ty = FusedAdam(x, **kw), torch.optim.AdamW(y, **kw)
-    handle = lambda: fx._lists.groups[0][4][0][4].get("prep")
+    handle = lambda: fx._lists.groups[0].buckets[0].handles.get("prep")
     g = torch.Generator(device="cuda").manual_seed(5)
     for p, q in zip(x, y):
         p.grad = torch.randn(p.shape, generator=g, device="cuda")
@@ -207,7 +207,7 @@ def test_fused_sgd_prepared_handle_follows_the_gradients():
         p.grad = torch.randn(p.shape, generator=g, device="cuda"); q.grad = p.grad.clone()
     for it in range(2):                                   # step 0 creates the momentum buffers, step 1 builds the memo
         fx.step(); ty.step()
-    handle = lambda: fx._sets[0][4][1][3].get("prep")    # the fp32 bucket
+    handle = lambda: fx._sets[0].buckets[1].handles.get("prep")    # the fp32 bucket
     hits0 = None
     for it in range(4):
         for p, q in zip(x, y):
@@ -246,7 +246,7 @@ def test_fused_lamb_prepared_handles_match_plain_lists(two_groups):
     kw = dict(lr=1e-2, weight_decay=0.01, max_grad_norm=0.5)
     groups = lambda ps: [{"params": ps[:4] + ps[6:]}, {"params": ps[4:6], "weight_decay": 0.0}] if two_groups else ps
     fx, fy = FusedLAMB(groups(x), **kw), FusedLAMB(groups(y), **kw)
-    fy._lists._maybe_prepare = lambda bucket, gs: [gs, bucket[1], bucket[2], bucket[3]]     # the twin never prepares
+    fy._lists._maybe_prepare = lambda bucket, gs: [gs, bucket.params, bucket.state0, bucket.state1]     # the twin never prepares
     g = torch.Generator(device="cuda").manual_seed(8)
 
     def fresh_grads(keep=None):
@@ -258,18 +258,19 @@ def test_fused_lamb_prepared_handles_match_plain_lists(two_groups):
     fresh_grads()
     fx.step(); fy.step()
     assert same(x, y, tol=0.0)
-    b0 = fx._lists.groups[0][4]
-    assert [b[1][0].dtype for b in b0] == [torch.float32, torch.float16]
-    assert all(b[4].get("prep") is not None and b[4].get("prep_g") is not None and b[4]["prep_g"].depth == 1 for b in b0)
-    assert all(b[4].get("prep") is None for b in fy._lists.groups[0][4])
-    first = [b[4]["prep_g"] for b in b0]
+    b0 = fx._lists.groups[0].buckets
+    assert [b.params[0].dtype for b in b0] == [torch.float32, torch.float16]
+    assert all(b.handles.get("prep") is not None and b.handles.get("prep_g") is not None and b.handles["prep_g"].depth == 1
+               for b in b0)
+    assert all(b.handles.get("prep") is None for b in fy._lists.groups[0].buckets)
+    first = [b.handles["prep_g"] for b in b0]
     up0 = mt.lib.b200mt_table_uploads()
     for it in range(3):                                   # in place (the update kernel has overwritten g): same handles
         for p, q in zip(x, y):
             p.grad.copy_(torch.randn(p.shape, generator=g, device="cuda")); q.grad.copy_(p.grad)
         fx.step(); fy.step()
         assert same(x, y, tol=0.0)
-        assert [b[4]["prep_g"] for b in fx._lists.groups[0][4]] == first
+        assert [b.handles["prep_g"] for b in fx._lists.groups[0].buckets] == first
     if not two_groups:                                    # nothing but the list of two norms can have been uploaded
         assert mt.lib.b200mt_table_uploads() - up0 <= 3
     keep = []
@@ -277,7 +278,7 @@ def test_fused_lamb_prepared_handles_match_plain_lists(two_groups):
         fresh_grads(keep)
         fx.step(); fy.step()
         assert same(x, y, tol=0.0)
-    assert all(b[4].get("prep") is None and b[4].get("prep_g") is None for b in fx._lists.groups[0][4])
+    assert all(b.handles.get("prep") is None and b.handles.get("prep_g") is None for b in fx._lists.groups[0].buckets)
     x[1].grad, y[1].grad = None, None                     # a parameter without gradient, then with one again
     fx.step(); fy.step()
     fresh_grads()
