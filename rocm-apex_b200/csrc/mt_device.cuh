@@ -155,6 +155,47 @@ __device__ __forceinline__ void st_f8(void* p, const float (&r)[8]) {
                :: "l"(p), "f"(r[0]), "f"(r[1]), "f"(r[2]), "f"(r[3]), "f"(r[4]), "f"(r[5]), "f"(r[6]), "f"(r[7])
                : "memory");
 }
+// ... with an L2 eviction priority: POL 1 = evict_first for data this kernel is the last to touch for a while, 2 = evict_last
+// for data the next kernel of the stream reads back.  PTX takes the qualifier itself on 256-bit accesses only; 128-bit
+// accesses carry it as a cache-hint policy operand (ends up in the access descriptor, two uniform registers).
+template <int POL> __device__ __forceinline__ unsigned long long l2_policy_word() {
+  unsigned long long pol;
+  if constexpr (POL == 1) asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  else asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+template <int POL> __device__ __forceinline__ void ld_f4_l2(const void* p, float (&r)[4]) {
+  asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]) : "l"(p), "l"(l2_policy_word<POL>()) : "memory");
+}
+template <int POL> __device__ __forceinline__ void st_f4_l2(void* p, const float (&r)[4]) {
+  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;"
+               :: "l"(p), "f"(r[0]), "f"(r[1]), "f"(r[2]), "f"(r[3]), "l"(l2_policy_word<POL>()) : "memory");
+}
+template <int POL> __device__ __forceinline__ void ld_f8_l2(const void* p, float (&r)[8]) {
+  if constexpr (POL == 1)
+    asm volatile("ld.global.L1::no_allocate.L2::evict_first.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]), "=f"(r[4]), "=f"(r[5]), "=f"(r[6]), "=f"(r[7])
+                 : "l"(p) : "memory");
+  else if constexpr (POL == 2)
+    asm volatile("ld.global.L1::no_allocate.L2::evict_last.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]), "=f"(r[4]), "=f"(r[5]), "=f"(r[6]), "=f"(r[7])
+                 : "l"(p) : "memory");
+  else
+    ld_f8(p, r);
+}
+template <int POL> __device__ __forceinline__ void st_f8_l2(void* p, const float (&r)[8]) {
+  if constexpr (POL == 1)
+    asm volatile("st.global.L1::no_allocate.L2::evict_first.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 :: "l"(p), "f"(r[0]), "f"(r[1]), "f"(r[2]), "f"(r[3]), "f"(r[4]), "f"(r[5]), "f"(r[6]), "f"(r[7])
+                 : "memory");
+  else if constexpr (POL == 2)
+    asm volatile("st.global.L1::no_allocate.L2::evict_last.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 :: "l"(p), "f"(r[0]), "f"(r[1]), "f"(r[2]), "f"(r[3]), "f"(r[4]), "f"(r[5]), "f"(r[6]), "f"(r[7])
+                 : "memory");
+  else
+    st_f8(p, r);
+}
 __device__ __forceinline__ uint4 ld_u4(const void* p) {
   uint4 r;
   asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -475,13 +516,20 @@ template <> struct Elem<mc_e5m2> {
 };
 
 // vector access of V = 4 or 8 elements
-template <typename T, int V> __device__ __forceinline__ void ldv(const void* p, float (&r)[V]) {
+// POL: L2 eviction priority (see ld_f8_l2); honoured for 256-bit fp32 vectors, ignored elsewhere
+template <typename T, int V, int POL = 0> __device__ __forceinline__ void ldv(const void* p, float (&r)[V]) {
   static_assert(V == 4 || V == 8, "vector width");
-  if constexpr (V == 4) Elem<T>::ld4(p, r); else Elem<T>::ld8(p, r);
+  if constexpr (V == 8 && POL != 0 && std::is_same<T, float>::value) ld_f8_l2<POL>(p, r);
+  else if constexpr (V == 4 && POL != 0 && std::is_same<T, float>::value) ld_f4_l2<POL>(p, r);
+  else if constexpr (V == 4) Elem<T>::ld4(p, r); else Elem<T>::ld8(p, r);
 }
-template <typename T, int V> __device__ __forceinline__ void stv(void* p, const float (&r)[V]) {
-  if constexpr (V == 4) Elem<T>::st4(p, r); else Elem<T>::st8(p, r);
+template <typename T, int V, int POL = 0> __device__ __forceinline__ void stv(void* p, const float (&r)[V]) {
+  if constexpr (V == 8 && POL != 0 && std::is_same<T, float>::value) st_f8_l2<POL>(p, r);
+  else if constexpr (V == 4 && POL != 0 && std::is_same<T, float>::value) st_f4_l2<POL>(p, r);
+  else if constexpr (V == 4) Elem<T>::st4(p, r); else Elem<T>::st8(p, r);
 }
+// per-list policy out of an op's two-bits-per-list word (list k in bits 2k, 2k+1)
+constexpr int l2_policy(unsigned word, int k) { return (int)((word >> (2 * k)) & 3u); }
 // required alignment, in bytes, of a V-element vector of T (element-wise types: just the element)
 template <typename T, int V> constexpr int vec_align() {
   return (Elem<T>::QUAD_ALIGN > Elem<T>::SIZE) ? Elem<T>::SIZE * V : Elem<T>::SIZE;
@@ -620,7 +668,7 @@ mt_stream_kernel(const TableView tv, const Op op) {
           static_for<NL>([&](auto k) {
             using T = typename Types::template at<k.value>;
             if (lmask & (1u << k.value)) {
-              ldv<T, V>(base[k.value] + ((size_t)head + (size_t)q * V) * Elem<T>::SIZE, x[u][k.value]);
+              ldv<T, V, l2_policy(Op::L2_LOADS, k.value)>(base[k.value] + ((size_t)head + (size_t)q * V) * Elem<T>::SIZE, x[u][k.value]);
             } else {
 #pragma unroll
               for (int i = 0; i < V; i++) x[u][k.value][i] = 0.f;
@@ -645,7 +693,7 @@ mt_stream_kernel(const TableView tv, const Op op) {
             using T = typename Types::template at<k.value>;
             if constexpr ((Op::STORES >> k.value) & 1u) {
               if (smask & (1u << k.value))
-                stv<T, V>(base[k.value] + ((size_t)head + (size_t)q * V) * Elem<T>::SIZE, x[u][k.value]);
+                stv<T, V, l2_policy(Op::L2_STORES, k.value)>(base[k.value] + ((size_t)head + (size_t)q * V) * Elem<T>::SIZE, x[u][k.value]);
             }
           });
         }
@@ -773,6 +821,7 @@ struct OpBase {
   static constexpr int UNROLL = 4;
   static constexpr int MIN_CTAS = 4;
   static constexpr int VEC = 4;
+  static constexpr unsigned L2_LOADS = 0, L2_STORES = 0;   // two bits per list: 0 none, 1 evict_first, 2 evict_last (ldv / stv)
   __device__ __forceinline__ unsigned store_mask() const { return 0xffffffffu; }
   template <class S> __device__ __forceinline__ bool begin(S&) const { return true; }
   template <class S> __device__ __forceinline__ void tile_begin(S&, const TileLoc&) const {}

@@ -32,6 +32,14 @@ int adam_tma_tile();
 int adam_tma_launch(const TableView& tv, float beta1, float beta2, float bc1, float bc2, float eps, float lr,
                     float decay, float grad_scale, int mode, cudaStream_t stream);
 
+// L2 eviction priority per list [g, p, m, v(, copy)], two bits each (mt_device.cuh: l2_policy)
+#ifndef B200MT_ADAM_L2_LOADS
+#define B200MT_ADAM_L2_LOADS 0
+#endif
+#ifndef B200MT_ADAM_L2_STORES
+#define B200MT_ADAM_L2_STORES 0
+#endif
+
 template <typename T> struct is_mc { static constexpr bool value = false; };
 template <> struct is_mc<mc_bf16> { static constexpr bool value = true; };
 template <> struct is_mc<mc_f16> { static constexpr bool value = true; };
@@ -49,6 +57,7 @@ struct AdamOp : OpBase {
   static constexpr int VEC = B200MT_ADAM_VEC;
   static constexpr int THREADS = 256;
   static constexpr int MIN_CTAS = (VEC * UNROLL > 8) ? 2 : 4;
+  static constexpr unsigned L2_LOADS = B200MT_ADAM_L2_LOADS, L2_STORES = B200MT_ADAM_L2_STORES;
   float beta1, beta2, bc1, bc2, eps, lr, decay, grad_scale;
   int mode;
   __device__ __forceinline__ unsigned load_mask() const { return 0b01111; }

@@ -23,6 +23,14 @@
 #define B200MT_AXPBY_UNROLL 2
 #endif
 
+// L2 eviction priority of [in, out], two bits per list (mt_device.cuh: l2_policy)
+#ifndef B200MT_SCALE_L2_LOADS
+#define B200MT_SCALE_L2_LOADS 0
+#endif
+#ifndef B200MT_SCALE_L2_STORES
+#define B200MT_SCALE_L2_STORES 0
+#endif
+
 namespace b200mt {
 
 __device__ __forceinline__ bool nonfinite(float v) {
@@ -41,6 +49,7 @@ struct ScaleOp : OpBase {
   static constexpr bool ANY16 = Elem<Tin>::SIZE == 2 || Elem<Tout>::SIZE == 2;
   static constexpr int UNROLL = ANY16 ? B200MT_SCALE_UNROLL : B200MT_SCALE32_UNROLL;
   static constexpr int VEC = ANY16 ? B200MT_SCALE_VEC : B200MT_SCALE32_VEC;
+  static constexpr unsigned L2_LOADS = B200MT_SCALE_L2_LOADS, L2_STORES = B200MT_SCALE_L2_STORES;
   struct State { bool bad = false; };
   float scale;
   int* noop;

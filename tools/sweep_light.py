@@ -83,6 +83,9 @@ e1.record(stream)
 torch.cuda.synchronize()
 r["resnet_warm_step_us"] = round(e0.elapsed_time(e1) * 1e3 / 200, 2)
 del g, p, m, v
+if os.environ.get("SWEEP_ONLY") == "resnet":       # just the headline list (A/B of a change to the scale / Adam kernels)
+    print(json.dumps(r))
+    sys.exit(0)
 
 # ---- mid-size lists
 for tag, T, n in (("1000x64K", 1000, 65536), ("100x1M", 100, 1 << 20)):
