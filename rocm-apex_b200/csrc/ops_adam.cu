@@ -56,7 +56,11 @@ struct AdamOp : OpBase {
   static constexpr int UNROLL = B200MT_ADAM_UNROLL;
   static constexpr int VEC = B200MT_ADAM_VEC;
   static constexpr int THREADS = 256;
+#ifdef B200MT_ADAM_MIN_CTAS
+  static constexpr int MIN_CTAS = B200MT_ADAM_MIN_CTAS;
+#else
   static constexpr int MIN_CTAS = (VEC * UNROLL > 8) ? 2 : 4;
+#endif
   static constexpr unsigned L2_LOADS = B200MT_ADAM_L2_LOADS, L2_STORES = B200MT_ADAM_L2_STORES;
   float beta1, beta2, bc1, bc2, eps, lr, decay, grad_scale;
   int mode;
