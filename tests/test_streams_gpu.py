@@ -74,3 +74,52 @@ def test_l2norm_scratch_is_per_stream():
     for (an, ap), (bn, bp) in res:
         assert abs(float(an) - 2.0 * (8 << 20) ** 0.5) < 1e-2 and abs(float(bn) - 3.0 * (8 << 20) ** 0.5) < 1e-2
         assert torch.allclose(ap, torch.full_like(ap, 2.0 * 1024.0)) and torch.allclose(bp, torch.full_like(bp, 3.0 * 1024.0))
+
+
+def test_host_threads_on_their_own_streams_share_the_library():
+    """Four host threads, each on its own stream, hammer the same library instance (ctypes drops the GIL inside a call, so the
+    calls really overlap): per-device lock, table cache (more distinct lists than it has slots, so slots are evicted under
+    the other threads' feet), per-stream scratch of the norm ops.  Every thread must see exactly what it would have seen alone."""
+    import threading
+
+    import amp_C
+    nthreads, rounds = 4, 60
+    errors = []
+
+    def worker(tid):
+        try:
+            torch.cuda.set_device(0)
+            stream = torch.cuda.Stream()
+            g = torch.Generator(device="cuda").manual_seed(100 + tid)
+            with torch.cuda.stream(stream):
+                f = torch.zeros(1, dtype=torch.int32, device="cuda")
+                # 30 list sets per thread -> 120 in flight against 64 cache slots
+                sets = []
+                for k in range(30):
+                    sizes = [1000 + 37 * k + 11 * tid, 5 + k, 70000 + tid]
+                    xs = [torch.randn(n, generator=g, device="cuda") for n in sizes]
+                    sets.append((xs, [torch.empty_like(x) for x in xs], float(torch.cat(xs).double().norm())))
+                for r in range(rounds):
+                    xs, outs, want = sets[(r * 7 + tid) % len(sets)]
+                    s = 0.5 + tid
+                    amp_C.multi_tensor_scale(CHUNK, f, [xs, outs], s)
+                    n, per = amp_C.multi_tensor_l2norm(CHUNK, f, [xs], True)
+                    n2, _ = amp_C.multi_tensor_l2norm(CHUNK, f, [outs], False)
+                    got, got2 = float(n), float(n2)           # synchronises this thread's stream only
+                    assert abs(got - want) <= 1e-5 * want, (tid, r, got, want)
+                    assert abs(got2 - s * want) <= 1e-5 * s * want, (tid, r, got2, s * want)
+                    for x, o, pn in zip(xs, outs, per.tolist()):
+                        assert torch.equal(o, x * s)
+                        assert abs(pn - float(x.double().norm())) <= 1e-5 * max(pn, 1e-30)
+                assert int(f) == 0
+        except Exception as e:                                # surfaces in the main thread
+            errors.append((tid, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(t,)) for t in range(nthreads)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=300)
+    torch.cuda.synchronize()
+    assert not any(t.is_alive() for t in threads), "a worker hung"
+    assert errors == [], errors
