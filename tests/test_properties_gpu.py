@@ -156,3 +156,28 @@ def test_lamb_trust_ratio_invariants(amp_C, shapes):
         assert abs(step_norm - lr * pn) <= 2e-4 * lr * pn + 1e-7 * pn    # p is fp32: the step is observed through rounding of p
         checked += 1
     assert checked > 100
+
+
+def test_one_tensor_longer_than_2_to_the_31_elements(amp_C):
+    """A single tensor of 2^31 + 4099 elements (the reference's TensorListMetadata keeps sizes in `int`,
+    csrc/multi_tensor_apply.cuh:16-26, and cannot take it; here numel and the tile offsets are 64-bit): the unscale touches
+    every element once, finds an inf behind the 2^31 boundary, and the norm of all-ones is sqrt(n)."""
+    n = (1 << 31) + 4099
+    x = torch.full((n,), 2.0, device="cuda", dtype=torch.float16)
+    probes = [0, 1, 4095, 4096, (1 << 31) - 1, 1 << 31, (1 << 31) + 1, n - 2, n - 1]
+    for k, i in enumerate(probes):
+        x[i] = float(k + 3)
+    f = torch.zeros(1, dtype=torch.int32, device="cuda")
+    amp_C.multi_tensor_scale(2048 * 32, f, [[x], [x]], 0.5)
+    assert int(f) == 0
+    for k, i in enumerate(probes):
+        assert float(x[i]) == 0.5 * (k + 3)
+        x[i] = 1.0
+    assert float(x.min()) == 1.0 and float(x.max()) == 1.0          # every other element was halved exactly once
+    norm, per = amp_C.multi_tensor_l2norm(2048 * 32, f, [[x]], True)
+    assert abs(float(norm) - n ** 0.5) <= 1e-5 * n ** 0.5 and abs(float(per[0]) - n ** 0.5) <= 1e-5 * n ** 0.5
+    assert int(f) == 0
+    x[(1 << 31) + 7] = float("inf")
+    y = torch.empty(n, device="cuda", dtype=torch.float16)
+    amp_C.multi_tensor_scale(2048 * 32, f, [[x], [y]], 1.0)
+    assert int(f) == 1 and float(y[n - 1]) == 1.0 and bool(torch.isinf(y[(1 << 31) + 7]))
