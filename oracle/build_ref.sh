@@ -81,7 +81,8 @@ rm -rf "$OBJ"
 # tests/test_reference_python_gpu.py and tests/test_reference_suite_gpu.py can run the reference's optimizer / amp classes and
 # its own unit tests on the GPU box -- once over this repo's amp_C shim and once over amp_C_ref -- and compare.
 # oracle/_ref/ is git-ignored: nothing of it enters the history.
-if [ ! -f "$OUT/pyref.zip" ] || [ ! -f "$OUT/pyref_tests.zip" ] || [ -n "${FORCE:-}" ]; then
+STAGE=2   # bump when the set of staged files changes
+if [ ! -f "$OUT/pyref.zip" ] || [ ! -f "$OUT/pyref_tests.zip" ] || [ "$(cat "$OUT/pyref.stage" 2>/dev/null)" != "$STAGE" ] || [ -n "${FORCE:-}" ]; then
   rm -rf "$OUT/pyref" "$OUT/pyref_tests" "$OUT/pyref.zip" "$OUT/pyref_tests.zip"
   mkdir -p "$OUT/pyref" "$OUT/pyref_tests"
   (cd "$REF" && find apex -name '*.py' | while read -r f; do mkdir -p "$OUT/pyref/$(dirname "$f")"; cp "$f" "$OUT/pyref/$f"; done)
@@ -89,12 +90,17 @@ if [ ! -f "$OUT/pyref.zip" ] || [ ! -f "$OUT/pyref_tests.zip" ] || [ -n "${FORCE
     mkdir -p "$OUT/pyref_tests/$d"
     cp "$REF"/tests/L0/$d/*.py "$OUT/pyref_tests/$d/"
   done
+  # the reference's two-rank scripts for the DDP bucket path and amp master weights (tests/distributed/*)
+  mkdir -p "$OUT/pyref_tests/distributed"
+  cp "$REF"/tests/distributed/DDP/ddp_race_condition_test.py "$REF"/tests/distributed/amp_master_params/amp_master_params.py \
+     "$REF"/tests/distributed/amp_master_params/compare.py "$OUT/pyref_tests/distributed/"
   $PY -W ignore -m compileall -q -b "$OUT/pyref" "$OUT/pyref_tests" > /dev/null 2>&1 || true   # files that do not compile under this Python are not on the path
   find "$OUT/pyref" "$OUT/pyref_tests" -name '*.py' -delete
   n=$(find "$OUT/pyref" "$OUT/pyref_tests" -name '*.pyc' | wc -l)
   # one importable archive each (zipimport reads sourceless .pyc): a single binary file travels with gpurun like the .so files
   (cd "$OUT/pyref" && $PY -m zipfile -c "$OUT/pyref.zip" apex)
-  (cd "$OUT/pyref_tests" && $PY -m zipfile -c "$OUT/pyref_tests.zip" run_amp run_optimizers)
+  (cd "$OUT/pyref_tests" && $PY -m zipfile -c "$OUT/pyref_tests.zip" run_amp run_optimizers distributed)
+  echo "$STAGE" > "$OUT/pyref.stage"
   rm -rf "$OUT/pyref" "$OUT/pyref_tests"
   echo "[oracle/build_ref] staged $n reference modules as bytecode in $OUT/pyref.zip, $OUT/pyref_tests.zip"
 fi
