@@ -1,6 +1,6 @@
 """Probe (not product): NCCL reduce-scatter / all-gather bandwidth on the flat bf16 layout, alone and
 concurrently on two communicators, and whether torch symmetric memory offers a multicast pointer."""
-import os, sys, time, json
+import os, json
 import torch, torch.distributed as dist
 
 def main():
