@@ -14,8 +14,10 @@ all-gather over NCCL, one process per GPU (launched by torch.distributed.run).
 ranks.  `e2e` is the same step through the public Python API with the step's gradients copied
 from pinned host memory and the overflow flag read back inside the timed region.  `roofline` is
 for the dominant kernel (the Adam read-modify-write, 28 B/param).  `cpu_baseline` / `--impl
-reference` time the reference's python-only build path (apex/amp/scaler.py:6-23,85-100 restated
-in oracle/mt_oracle.py + stock torch.optim.Adam) on this box's host cores.
+reference` time the reference's python-only build path on this box's host cores: the reference's own
+`LossScaler.unscale_python` (apex/amp/scaler.py:6-23,85-100, from the bytecode archive oracle/_ref/pyref.zip
+that oracle/build_ref.sh stages; kind "reference") + stock torch.optim.Adam -- or, where that archive is
+absent, its restatement in oracle/mt_oracle.py (kind "port").
 """
 import argparse
 import json
@@ -160,8 +162,48 @@ def single_config(nparams, ntensors):
             "algorithmic_bytes_per_step": 36 * nparams}
 
 
-def cpu_reference_run(steps, warmup, max_seconds=30.0, shapes=None):
+def reference_unscale_python():
+    """-> (unscale(grads) -> overflow, kind).  kind "reference": the reference's OWN `LossScaler.unscale_python` and
+    `scale_check_overflow_python` (apex/amp/scaler.py:6-23,85-100), imported from the bytecode archive oracle/build_ref.sh stages
+    from /root/reference (oracle/_ref/pyref.zip; it travels to the GPU box like the compiled checkers), with no fused back end
+    importable so that the package takes its python-only path.  Only in a process that has imported neither this repo's
+    `apex` mirror nor its `amp_C`; otherwise, or without the archive, kind "port": the restatement in oracle/mt_oracle.py."""
     from oracle import mt_oracle as O
+    archive = os.path.join(ROOT, "oracle", "_ref", "pyref.zip")
+    if os.path.exists(archive) and "apex" not in sys.modules and "amp_C" not in sys.modules:
+        saved_path, saved_mods = list(sys.path), dict(sys.modules)
+        try:
+            import collections.abc
+            import types
+            six = types.ModuleType("torch._six")        # removed from torch 2.x; apex/amp/_initialize.py:2 imports it
+            six.string_classes, six.container_abcs = (str, bytes), collections.abc
+            sys.modules["torch._six"] = six
+            sys.modules["amp_C"] = None                 # `import amp_C` raises ImportError: the reference's python-only build
+            sys.path[:] = [archive] + [q for q in sys.path if not q.rstrip("/").endswith("rocm-apex_b200")]
+            from apex.amp.scaler import LossScaler
+            from apex.multi_tensor_apply import multi_tensor_applier
+            assert not multi_tensor_applier.available
+            import apex
+            assert os.path.realpath(apex.__file__).startswith(os.path.realpath(archive)), apex.__file__
+
+            def unscale(grads):
+                # the scaler's state as LossScaler.__init__("dynamic") leaves it (:52-60); the constructor itself allocates a
+                # CUDA flag buffer (:65) that the python-only path never touches
+                me = types.SimpleNamespace(dynamic=True, _has_overflow=False)
+                LossScaler.unscale_python(me, grads, grads, LOSS_SCALE)
+                return me._has_overflow
+            return unscale, "reference"
+        except Exception as e:                          # archive from another Python version, ...: fall back to the port
+            sys.stderr.write("bench.py: staged reference not usable (%r); timing the oracle port\n" % (e,))
+            sys.path[:] = saved_path
+            for k in list(sys.modules):
+                if k not in saved_mods and (k == "apex" or k.startswith("apex.") or k in ("amp_C", "torch._six")):
+                    del sys.modules[k]
+    return (lambda grads: O.unscale_python(grads, grads, LOSS_SCALE, dynamic=True)), "port"
+
+
+def cpu_reference_run(steps, warmup, max_seconds=30.0, shapes=None):
+    unscale, kind = reference_unscale_python()
     # torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm is meant to use all the host threads it CAN use: the
     # count is calibrated on a short probe (every thread the affinity mask allows, half, a quarter, one), because on a
     # box whose mask is wider than its usable cores the full count runs 50x slower than half of it
@@ -198,7 +240,7 @@ def cpu_reference_run(steps, warmup, max_seconds=30.0, shapes=None):
             p.grad.copy_(g)          # "backward" leaves scaled grads; not part of the reference path cost
         t0 = time.perf_counter()
         grads = [p.grad for p in params]
-        overflow = O.unscale_python(grads, grads, LOSS_SCALE, dynamic=True)   # apex/amp/scaler.py:85-100
+        overflow = unscale(grads)                                             # apex/amp/scaler.py:85-100
         if not overflow:
             opt.step()
         return time.perf_counter() - t0
@@ -213,7 +255,25 @@ def cpu_reference_run(steps, warmup, max_seconds=30.0, shapes=None):
             break
     ms = 1e3 * sum(times) / len(times)
     return {"value": nparams / (ms * 1e-3), "ms_per_step": ms, "steps": len(times), "cores": torch.get_num_threads(),
-            "host_cpus": os.cpu_count(), "nparams": nparams}
+            "host_cpus": os.cpu_count(), "nparams": nparams, "kind": kind}
+
+
+def cpu_baseline_leg(steps, warmup, max_seconds):
+    """The `cpu_baseline` of this repo's own N = 1 line: the reference arm run as a child process (this process has this repo's
+    amp_C loaded, and the reference's package must not find a fused back end), bounded to `max_seconds` of stepping."""
+    drop = ("RANK", "LOCAL_RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE", "GROUP_RANK", "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS",
+            "TORCHELASTIC_RUN_ID")
+    env = {k: v for k, v in os.environ.items() if k not in drop}
+    try:
+        r = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", str(steps), "--warmup",
+                            str(warmup), "--max-seconds", str(max_seconds)], capture_output=True, text=True, timeout=600, env=env)
+        line = json.loads([x for x in r.stdout.splitlines() if x.startswith("{")][-1])
+        c = line["cpu_baseline"]
+        return {"value": c["value"], "cores": c["cores"], "steps": c["steps"], "host_cpus": c["host_cpus"],
+                "ms_per_step": c["ms_per_step"], "kind": c["kind"]}
+    except Exception as e:
+        sys.stderr.write("bench.py: reference arm as a child process failed (%r); timing the oracle port in process\n" % (e,))
+        return cpu_reference_run(steps=steps, warmup=warmup, max_seconds=max_seconds)
 
 
 def run_reference_arm(args):
@@ -226,7 +286,7 @@ def run_reference_arm(args):
         # unscale + torch.optim.Adam on a bounded sample of it (the four attention projections of layer 0)
         full = param_shapes.llama3_8b()
         shapes = full[1:10]             # one whole decoder layer: q/k/v/o, gate/up/down, two norms = 218 M parameters
-        r = cpu_reference_run(args.steps, args.warmup, max_seconds=120.0, shapes=shapes)
+        r = cpu_reference_run(args.steps, args.warmup, max_seconds=args.max_seconds, shapes=shapes)
         sample = "%d steps over a %d-parameter sample (decoder layer 0) of the Llama-3-8B list on %d host threads " \
                  "(torch.set_num_threads overrides torchrun's OMP_NUM_THREADS=1); value = sample params / step time" % (
                      r["steps"], r["nparams"], r["cores"])
@@ -235,7 +295,7 @@ def run_reference_arm(args):
                   "tensors": len(full), "params": param_shapes.numel(full), "parallelism": "zero-dp%d" % world}
         scaling = "strong"
     else:
-        r = cpu_reference_run(args.steps, args.warmup, max_seconds=120.0)
+        r = cpu_reference_run(args.steps, args.warmup, max_seconds=args.max_seconds)
         sample = "%d full steps of the ResNet-50 list (161 tensors, %d params) on %d host threads" % (r["steps"], r["nparams"], r["cores"])
         config = single_config(r["nparams"], 161)
         scaling = "weak"
@@ -244,8 +304,10 @@ def run_reference_arm(args):
         "steps": r["steps"], "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
         "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": config,
-        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample,
-                         "host_cpus": r["host_cpus"]},
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": sample,
+                         "host_cpus": r["host_cpus"], "ms_per_step": r["ms_per_step"], "steps": r["steps"],
+                         "unscale": "the reference's own LossScaler.unscale_python (oracle/_ref/pyref.zip)" if r["kind"] == "reference"
+                                    else "oracle/mt_oracle.py restatement of LossScaler.unscale_python"},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -746,7 +808,7 @@ def run_single(args):
     if os.environ.get("B200MT_BENCH_SKIP_CPU"):   # profiling runs only: keep the command short under ncu
         cpu = {"value": None, "cores": 0, "steps": 0, "host_cpus": os.cpu_count(), "ms_per_step": None}
     else:
-        cpu = cpu_reference_run(steps=40, warmup=2, max_seconds=20.0)
+        cpu = cpu_baseline_leg(steps=40, warmup=2, max_seconds=20.0)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -758,7 +820,7 @@ def run_single(args):
                      "kernel": "mt_stream_kernel<AdamOp<float,float,float,false>>",
                      "bytes_per_launch": adam_bytes, "avg_launch_ms": adam_avg, "peak_source": peak_src,
                      "frac_of_8TBs_nominal": achieved / 8000.0},
-        "cpu_baseline": {"value": cpu["value"], "unit": UNIT, "cores": cpu["cores"], "kind": "port",
+        "cpu_baseline": {"value": cpu["value"], "unit": UNIT, "cores": cpu["cores"], "kind": cpu.get("kind", "port"),
                          "sample": "%d steps of the same ResNet-50 list on host CPU (python-only unscale + torch.optim.Adam)" % cpu["steps"],
                          "host_cpus": cpu["host_cpus"], "ms_per_step": cpu["ms_per_step"]},
         "e2e": {"value": nparams / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 4 * nparams, "d2h_bytes_per_step": 4,
@@ -794,6 +856,7 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--max-seconds", type=float, default=120.0, help="reference arm: stop stepping after this long")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
