@@ -39,3 +39,15 @@ def test_reference_arm_under_a_two_rank_launch_prints_from_rank_0_only():
     d = json.loads(lines[0])
     assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["config"]["params"] == 8030261248
     assert "sample" in d["cpu_baseline"] and d["cpu_baseline"]["cores"] >= 1
+
+
+def test_own_arm_refuses_to_run_without_a_gpu():
+    """The product path has no CPU fallback: on a box without a CUDA device `python bench.py` must say so and fail."""
+    import pytest
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "1"], capture_output=True,
+                       text=True, timeout=300, cwd=ROOT)
+    assert r.returncode != 0 and "no CPU fallback" in (r.stdout + r.stderr)
+    assert not [x for x in r.stdout.splitlines() if x.startswith("{")]
